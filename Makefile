@@ -1,0 +1,46 @@
+# Top-level build: libdpsvm.so (CUDA, sm_100a), the host C++ layer and CLI, the oracle (checker).
+#   make            everything
+#   make lib        dpsvm_b200/libdpsvm.so only
+NVCC      ?= nvcc
+CXX       := g++
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unknown-pragmas
+CSRC      := dpsvm_b200/csrc
+OBJDIR    := build
+LIB       := dpsvm_b200/libdpsvm.so
+CU_SRCS   := $(CSRC)/smo_kernels.cu $(CSRC)/dpsvm_ctx.cu $(CSRC)/predict.cu $(CSRC)/comm.cu $(CSRC)/host_utils.cu
+CU_OBJS   := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS))
+HDRS      := $(wildcard $(CSRC)/*.cuh) include/dpsvm_cuda.h
+
+HOST      := dpsvm_b200/host
+HOST_SRCS := $(HOST)/svmTrain.cpp $(HOST)/parse.cpp $(HOST)/model_io.cpp
+HOST_LIB  := dpsvm_b200/libdpsvm_host.so
+CLI       := dpsvm_b200/svmTrain
+
+all: lib host oracle
+
+lib: $(LIB)
+
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(LIB): $(CU_OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(CU_OBJS) -lcudart -ldl
+
+host: $(HOST_LIB) $(CLI)
+
+$(HOST_LIB): $(HOST_SRCS) $(wildcard include/*.h include/*.hpp) $(LIB)
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -shared -Iinclude -o $@ $(HOST_SRCS) -Ldpsvm_b200 -ldpsvm -Wl,-rpath,'$$ORIGIN'
+
+$(CLI): $(HOST)/svmTrainMain.cpp $(HOST_LIB)
+	$(CXX) -O2 -std=c++17 -Wall -Iinclude -o $@ $(HOST)/svmTrainMain.cpp -Ldpsvm_b200 -ldpsvm_host -ldpsvm -Wl,-rpath,'$$ORIGIN'
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -rf $(OBJDIR) $(LIB) $(HOST_LIB) $(CLI)
+	$(MAKE) -C oracle clean
+
+.PHONY: all lib host oracle clean

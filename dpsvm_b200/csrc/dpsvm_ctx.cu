@@ -1,0 +1,536 @@
+// dpsvm_ctx.cu -- the trainer context behind include/dpsvm_cuda.h: owns one rank's device state,
+// builds the CUDA graph of the device-resident SMO loop, and implements the extern "C" entry points.
+#include <limits.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <new>
+#include <vector>
+
+#include "dpsvm_internal.cuh"
+
+namespace dpsvm {
+
+static thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess)                                                                      \
+            return fail(e__ == cudaErrorMemoryAllocation ? DPSVM_ERR_NOMEM : DPSVM_ERR_CUDA,         \
+                        "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));       \
+    } while (0)
+
+static int env_int(const char* name, int dflt)
+{
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// ---------------------------------------------------------------------------------------------
+static void free_all(dpsvm_ctx* c)
+{
+    if (c->gexec) cudaGraphExecDestroy(c->gexec);
+    if (c->graph) cudaGraphDestroy(c->graph);
+    cudaFree(c->d_x); cudaFree(c->d_xsq); cudaFree(c->d_y); cudaFree(c->d_alpha); cudaFree(c->d_f);
+    cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_st);
+    cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
+    cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
+    predict_free(c);
+    comm_free(c);
+    if (c->h_st) cudaFreeHost(c->h_st);
+    if (c->h_keys) cudaFreeHost(c->h_keys);
+    if (c->h_small) cudaFreeHost(c->h_small);
+    for (int i = 0; i < 2; ++i) if (c->ev_slot[i]) cudaEventDestroy(c->ev_slot[i]);
+    if (c->ev_t0) cudaEventDestroy(c->ev_t0);
+    if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+}
+
+PassDev make_pass_args(dpsvm_ctx* c)
+{
+    PassDev a{};
+    const int off = c->p.shard_start - c->res0;   // owned rows inside the resident range
+    a.x4 = reinterpret_cast<const float4*>(c->d_x + (size_t)off * c->pitch);
+    a.n = c->p.shard_rows;
+    a.pitch4 = c->pitch / 4;
+    a.xsq = c->d_xsq + off;
+    a.y = c->d_y + off;
+    a.alpha = c->d_alpha + off;
+    a.f = c->d_f;
+    a.x_hi4 = reinterpret_cast<const float4*>(c->d_sel_rows);
+    a.x_lo4 = reinterpret_cast<const float4*>(c->d_sel_rows + c->pitch);
+    a.gamma = c->p.gamma;
+    a.c = c->p.c;
+    a.index_base = c->p.shard_start;
+    a.keys = c->d_keys;
+    a.dev = &c->d_st->pass;
+    return a;
+}
+
+CtlDev make_ctl_args(dpsvm_ctx* c)
+{
+    CtlDev a{};
+    a.st = c->d_st;
+    a.keys = c->d_keys;
+    a.x = c->d_x;
+    a.pitch = c->pitch;
+    a.res0 = c->res0;
+    a.xsq = c->d_xsq;
+    a.y = c->d_y;
+    a.alpha = c->d_alpha;
+    a.sel_rows = c->d_sel_rows;
+    a.c = c->p.c;
+    a.gamma = c->p.gamma;
+    a.epsilon = c->p.epsilon;
+    a.max_iter = c->p.max_iter;
+    a.cache = c->cache;
+    return a;
+}
+
+static int launch_iteration(dpsvm_ctx* c, cudaStream_t s)
+{
+    if (c->world > 1) return comm_launch_iteration(c, s);
+    CU(launch_control(make_ctl_args(c), s));
+    CU(launch_pass(make_pass_args(c), c->variant, s));
+    return DPSVM_OK;
+}
+
+static int build_graph(dpsvm_ctx* c)
+{
+    if (c->gexec) return DPSVM_OK;
+    CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = DPSVM_OK;
+    for (int i = 0; i < c->chunk && rc == DPSVM_OK; ++i) rc = launch_iteration(c, c->stream);
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+    if (rc != DPSVM_OK) { if (g) cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    c->graph = g;
+    CU(cudaGraphInstantiate(&c->gexec, c->graph, 0));
+    return DPSVM_OK;
+}
+
+static int launch_chunk(dpsvm_ctx* c)
+{
+    if (c->p.flags & DPSVM_FLAG_NO_GRAPH) {
+        for (int i = 0; i < c->chunk; ++i) {
+            int rc = launch_iteration(c, c->stream);
+            if (rc != DPSVM_OK) return rc;
+        }
+        return DPSVM_OK;
+    }
+    int rc = build_graph(c);
+    if (rc != DPSVM_OK) return rc;
+    CU(cudaGraphLaunch(c->gexec, c->stream));
+    return DPSVM_OK;
+}
+
+static int set_stop_at(dpsvm_ctx* c, int stop_at)
+{
+    // pageable source: cudaMemcpyAsync stages the 4 bytes before returning, so a stack variable is
+    // safe and the copy stays ordered with the graph launches on the stream.
+    int v = stop_at;
+    CU(cudaMemcpyAsync(&c->d_st->stop_at, &v, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    c->stop_at = stop_at;
+    return DPSVM_OK;
+}
+
+static void fill_status(const DevState& s, float ms, dpsvm_train_status* out)
+{
+    if (!out) return;
+    out->num_iter = s.num_iter;
+    out->converged = s.converged;
+    out->b_hi = s.b_hi;
+    out->b_lo = s.b_lo;
+    out->b = (s.b_lo + s.b_hi) / 2;     // svmTrainMain.cpp:329
+    out->cache_hits = s.cache_hits;
+    out->cache_lookups = s.cache_lookups;
+    out->last_chunk_ms = ms;
+    out->i_hi = s.i_hi;
+    out->i_lo = s.i_lo;
+    out->eta = s.eta;
+}
+
+static int init_cache(dpsvm_ctx* c)
+{
+    CacheDev& k = c->cache;
+    if (k.lines <= 0) return DPSVM_OK;
+    CU(cudaMemsetAsync(k.line_of_key, 0xFF, sizeof(int) * (size_t)c->p.num_train_data, c->stream));
+    CU(cudaMemsetAsync(k.meta, 0, sizeof(int) * kCacheMetaInts, c->stream));
+    const int minus1[2] = {-1, -1};   // pageable source: staged before the call returns
+    CU(cudaMemcpyAsync(k.meta + kCacheHead, minus1, 2 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    return DPSVM_OK;
+}
+
+// alpha = 0, f = -y, first selection, state cleared.
+static int reset_state(dpsvm_ctx* c)
+{
+    const int off = c->p.shard_start - c->res0;
+    CU(cudaMemsetAsync(c->d_alpha, 0, sizeof(float) * (size_t)c->res_n, c->stream));
+    CU(launch_init_state(c->d_y + off, c->p.shard_rows, nullptr, c->d_f, c->stream));
+    CU(cudaMemsetAsync(c->d_st, 0, sizeof(DevState), c->stream));
+    int rc = set_stop_at(c, INT_MAX);
+    if (rc != DPSVM_OK) return rc;
+    rc = init_cache(c);
+    if (rc != DPSVM_OK) return rc;
+    CU(launch_select(c->d_alpha + off, c->d_y + off, c->d_f, c->p.shard_rows, c->p.c, c->p.shard_start,
+                     c->d_keys, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->target_iter = 0;
+    return DPSVM_OK;
+}
+
+}  // namespace dpsvm
+
+using namespace dpsvm;
+
+// =================================================================================================
+// extern "C"
+// =================================================================================================
+extern "C" {
+
+const char* dpsvm_last_error(void) { return g_err; }
+int dpsvm_abi_version(void) { return DPSVM_ABI_VERSION; }
+
+int dpsvm_row_norms(const float* d_x, int n, int d, int pitch, float* d_xsq, void* stream)
+{
+    if (!d_x || !d_xsq || n < 0 || d <= 0 || pitch < d || pitch % 4) return fail(DPSVM_ERR_INVALID, "dpsvm_row_norms: bad arguments");
+    CU(launch_row_norms(d_x, n, pitch, d_xsq, (cudaStream_t)stream));
+    return DPSVM_OK;
+}
+
+int dpsvm_init_state(const int32_t* d_y, int n, float* d_alpha, float* d_f, void* stream)
+{
+    if (!d_y || !d_f || n < 0) return fail(DPSVM_ERR_INVALID, "dpsvm_init_state: bad arguments");
+    CU(launch_init_state(d_y, n, d_alpha, d_f, (cudaStream_t)stream));
+    return DPSVM_OK;
+}
+
+int dpsvm_select(const float* d_alpha, const int32_t* d_y, const float* d_f, int n, float c, int index_base,
+                 uint64_t* d_keys, void* stream)
+{
+    if (!d_alpha || !d_y || !d_f || !d_keys || n < 0) return fail(DPSVM_ERR_INVALID, "dpsvm_select: bad arguments");
+    CU(launch_select(d_alpha, d_y, d_f, n, c, index_base, reinterpret_cast<unsigned long long*>(d_keys), (cudaStream_t)stream));
+    return DPSVM_OK;
+}
+
+int dpsvm_smo_pass(const dpsvm_pass_args* g, void* stream)
+{
+    if (!g || !g->d_x || !g->d_xsq || !g->d_y || !g->d_alpha || !g->d_f || !g->d_x_hi || !g->d_x_lo || !g->d_keys)
+        return fail(DPSVM_ERR_INVALID, "dpsvm_smo_pass: null pointer");
+    if (g->n < 0 || g->d <= 0 || g->pitch < g->d || g->pitch % 4)
+        return fail(DPSVM_ERR_INVALID, "dpsvm_smo_pass: bad shape (pitch must be a multiple of 4 and >= d)");
+    PassDev a{};
+    a.x4 = reinterpret_cast<const float4*>(g->d_x);
+    a.n = g->n; a.pitch4 = g->pitch / 4;
+    a.xsq = g->d_xsq; a.y = g->d_y; a.alpha = g->d_alpha; a.f = g->d_f;
+    a.x_hi4 = reinterpret_cast<const float4*>(g->d_x_hi);
+    a.x_lo4 = reinterpret_cast<const float4*>(g->d_x_lo);
+    a.gamma = g->gamma; a.c = g->c; a.index_base = g->index_base;
+    a.keys = reinterpret_cast<unsigned long long*>(g->d_keys);
+    a.imm.active = 1; a.imm.both_hit = 0;
+    a.imm.delta_hi = g->delta_hi; a.imm.delta_lo = g->delta_lo;
+    a.imm.xsq_hi = g->xsq_hi; a.imm.xsq_lo = g->xsq_lo;
+    a.imm.line_hi = g->d_line_hi; a.imm.line_lo = g->d_line_lo;
+    a.dev = nullptr;
+    CU(launch_pass(a, g->variant, (cudaStream_t)stream));
+    return DPSVM_OK;
+}
+
+int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
+{
+    if (!p || !out) return fail(DPSVM_ERR_INVALID, "dpsvm_create: null argument");
+    if (p->num_attributes <= 0 || p->num_train_data <= 0) return fail(DPSVM_ERR_INVALID, "dpsvm_create: num_attributes and num_train_data must be positive");
+    if (p->shard_rows <= 0 || p->shard_start < 0 || p->shard_start + (long long)p->shard_rows > p->num_train_data)
+        return fail(DPSVM_ERR_INVALID, "dpsvm_create: shard [%d,+%d) outside [0,%d)", p->shard_start, p->shard_rows, p->num_train_data);
+    if (p->cache_size < 0) return fail(DPSVM_ERR_INVALID, "dpsvm_create: cache_size < 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
+        return fail(DPSVM_ERR_CUDA, "dpsvm_create: no CUDA device (this library has no CPU path)");
+    dpsvm_ctx* c = new (std::nothrow) dpsvm_ctx();
+    if (!c) return fail(DPSVM_ERR_NOMEM, "dpsvm_create: host allocation failed");
+    c->p = *p;
+    if (p->device >= 0) {
+        cudaError_t e = cudaSetDevice(p->device);
+        if (e != cudaSuccess) { delete c; return fail(DPSVM_ERR_CUDA, "cudaSetDevice(%d): %s", p->device, cudaGetErrorString(e)); }
+    }
+    cudaGetDevice(&c->device);
+    c->pitch = dpsvm_pitch_for(p->num_attributes);
+    const bool shard_only = (p->flags & DPSVM_FLAG_X_SHARD_ONLY) != 0;
+    c->res0 = shard_only ? p->shard_start : 0;
+    c->res_n = shard_only ? p->shard_rows : p->num_train_data;
+    c->chunk = env_int("DPSVM_CHUNK", 128);
+    if (c->chunk < 1) c->chunk = 1;
+    c->variant = env_int("DPSVM_VARIANT", 0);
+    c->world = 1; c->rank = 0;
+    // the reference with one line aliases the hi and lo buffers (latent bug, cache.cu:82-105): a
+    // single line cannot hold both rows of an iteration, so 1 behaves as "cache off" here.
+    c->cache.lines = p->cache_size >= 2 ? p->cache_size : 0;
+    c->cache.line_stride = ((size_t)p->shard_rows + 31) / 32 * 32;
+
+#define CUC(call)                                                                                        \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess) {                                                                        \
+            int code = fail(e__ == cudaErrorMemoryAllocation ? DPSVM_ERR_NOMEM : DPSVM_ERR_CUDA,         \
+                            "dpsvm_create: %s -> %s", #call, cudaGetErrorString(e__));                   \
+            free_all(c); delete c; return code;                                                          \
+        }                                                                                                \
+    } while (0)
+
+    CUC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CUC(cudaEventCreate(&c->ev_t0));
+    CUC(cudaEventCreate(&c->ev_t1));
+    for (int i = 0; i < 2; ++i) CUC(cudaEventCreateWithFlags(&c->ev_slot[i], cudaEventDisableTiming));
+    CUC(cudaMalloc(&c->d_x, sizeof(float) * (size_t)c->res_n * c->pitch));
+    CUC(cudaMalloc(&c->d_xsq, sizeof(float) * (size_t)c->res_n));
+    CUC(cudaMalloc(&c->d_y, sizeof(int) * (size_t)c->res_n));
+    CUC(cudaMalloc(&c->d_alpha, sizeof(float) * (size_t)c->res_n));
+    CUC(cudaMalloc(&c->d_f, sizeof(float) * (size_t)p->shard_rows));
+    CUC(cudaMalloc(&c->d_sel_rows, sizeof(float) * 2 * (size_t)c->pitch));
+    CUC(cudaMalloc(&c->d_ext_rows, sizeof(float) * 2 * (size_t)c->pitch));
+    CUC(cudaMalloc(&c->d_keys, 2 * sizeof(unsigned long long)));
+    CUC(cudaMalloc(&c->d_st, sizeof(DevState)));
+    CUC(cudaMallocHost(&c->h_st, 2 * sizeof(DevState)));
+    CUC(cudaMallocHost(&c->h_keys, 2 * sizeof(unsigned long long)));
+    CUC(cudaMallocHost(&c->h_small, 16 * sizeof(int)));
+    if (c->cache.lines > 0) {
+        CUC(cudaMalloc(&c->cache.data, sizeof(float) * c->cache.line_stride * (size_t)c->cache.lines));
+        CUC(cudaMalloc(&c->cache.line_of_key, sizeof(int) * (size_t)p->num_train_data));
+        CUC(cudaMalloc(&c->cache.key_of_line, sizeof(int) * (size_t)c->cache.lines));
+        CUC(cudaMalloc(&c->cache.prev, sizeof(int) * (size_t)c->cache.lines));
+        CUC(cudaMalloc(&c->cache.next, sizeof(int) * (size_t)c->cache.lines));
+        CUC(cudaMalloc(&c->cache.meta, sizeof(int) * kCacheMetaInts));
+    }
+#undef CUC
+    *out = c;
+    return DPSVM_OK;
+}
+
+int dpsvm_destroy(dpsvm_ctx* c)
+{
+    if (!c) return DPSVM_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_all(c);
+    delete c;
+    return DPSVM_OK;
+}
+
+static int finish_upload(dpsvm_ctx* c)
+{
+    CU(launch_row_norms(c->d_x, c->res_n, c->pitch, c->d_xsq, c->stream));
+    c->uploaded = true;
+    return reset_state(c);
+}
+
+int dpsvm_upload(dpsvm_ctx* c, const float* h_x, const int32_t* h_y)
+{
+    if (!c || !h_x || !h_y) return fail(DPSVM_ERR_INVALID, "dpsvm_upload: null argument");
+    CU(cudaSetDevice(c->device));
+    const int d = c->p.num_attributes;
+    if (c->pitch != d) CU(cudaMemsetAsync(c->d_x, 0, sizeof(float) * (size_t)c->res_n * c->pitch, c->stream));
+    CU(cudaMemcpy2DAsync(c->d_x, sizeof(float) * (size_t)c->pitch, h_x, sizeof(float) * (size_t)d, sizeof(float) * (size_t)d,
+                         (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_y, h_y, sizeof(int) * (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+    return finish_upload(c);
+}
+
+int dpsvm_upload_device(dpsvm_ctx* c, const float* d_x_shard, int pitch, const int32_t* d_y_shard)
+{
+    if (!c || !d_x_shard || !d_y_shard) return fail(DPSVM_ERR_INVALID, "dpsvm_upload_device: null argument");
+    if (!(c->p.flags & DPSVM_FLAG_X_SHARD_ONLY) && c->p.shard_rows != c->p.num_train_data)
+        return fail(DPSVM_ERR_STATE, "dpsvm_upload_device needs DPSVM_FLAG_X_SHARD_ONLY (or a single shard)");
+    if (pitch != c->pitch) return fail(DPSVM_ERR_INVALID, "dpsvm_upload_device: pitch %d, expected %d", pitch, c->pitch);
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(c->d_x, d_x_shard, sizeof(float) * (size_t)c->res_n * c->pitch, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_y, d_y_shard, sizeof(int) * (size_t)c->res_n, cudaMemcpyDeviceToDevice, c->stream));
+    return finish_upload(c);
+}
+
+int dpsvm_reset(dpsvm_ctx* c)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_reset: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_reset before dpsvm_upload");
+    CU(cudaSetDevice(c->device));
+    return reset_state(c);
+}
+
+int dpsvm_step1(dpsvm_ctx* c, float rv[4], uint64_t keys[2])
+{
+    if (!c || !rv) return fail(DPSVM_ERR_INVALID, "dpsvm_step1: null argument");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_step1 before dpsvm_upload");
+    CU(cudaMemcpyAsync(c->h_keys, c->d_keys, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    float f_hi, f_lo; int32_t i_hi, i_lo;
+    unpack_key_up(c->h_keys[0], &f_hi, &i_hi);
+    unpack_key_low(c->h_keys[1], &f_lo, &i_lo);
+    // an empty local set reports what the reference's reduction init does: index -1, +-1e9 (svmTrain.cu:312-315)
+    if (c->h_keys[0] == DPSVM_KEY_EMPTY) i_hi = -1;
+    if (c->h_keys[1] == DPSVM_KEY_EMPTY) i_lo = -1;
+    rv[0] = (float)i_hi; rv[1] = (float)i_lo; rv[2] = f_hi; rv[3] = f_lo;     // svmTrain.cu:478-481
+    if (keys) { keys[0] = c->h_keys[0]; keys[1] = c->h_keys[1]; }
+    return DPSVM_OK;
+}
+
+int dpsvm_step2(dpsvm_ctx* c, int i_hi, int i_lo, float alpha_hi_new, float alpha_lo_new,
+                const float* h_x_hi, const float* h_x_lo)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_step2: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_step2 before dpsvm_upload");
+    const int N = c->p.num_train_data;
+    if (i_hi < 0 || i_hi >= N || i_lo < 0 || i_lo >= N) return fail(DPSVM_ERR_INVALID, "dpsvm_step2: index out of range");
+    const bool hi_res = i_hi >= c->res0 && i_hi < c->res0 + c->res_n;
+    const bool lo_res = i_lo >= c->res0 && i_lo < c->res0 + c->res_n;
+    if ((!hi_res && !h_x_hi) || (!lo_res && !h_x_lo))
+        return fail(DPSVM_ERR_INVALID, "dpsvm_step2: row not resident on this rank and no host row supplied");
+    if (!hi_res || !lo_res)
+        return fail(DPSVM_ERR_STATE, "dpsvm_step2: non-resident rows need the fused multi-GPU loop (dpsvm_train)");
+    CU(cudaSetDevice(c->device));
+    CtlDev a = make_ctl_args(c);
+    a.directed = 1; a.dir_i_hi = i_hi; a.dir_i_lo = i_lo; a.dir_a_hi = alpha_hi_new; a.dir_a_lo = alpha_lo_new;
+    const int d = c->p.num_attributes;
+    if (h_x_hi) {
+        CU(cudaMemsetAsync(c->d_ext_rows, 0, sizeof(float) * (size_t)c->pitch, c->stream));
+        CU(cudaMemcpyAsync(c->d_ext_rows, h_x_hi, sizeof(float) * (size_t)d, cudaMemcpyHostToDevice, c->stream));
+        a.ext_row_hi = c->d_ext_rows;
+    }
+    if (h_x_lo) {
+        CU(cudaMemsetAsync(c->d_ext_rows + c->pitch, 0, sizeof(float) * (size_t)c->pitch, c->stream));
+        CU(cudaMemcpyAsync(c->d_ext_rows + c->pitch, h_x_lo, sizeof(float) * (size_t)d, cudaMemcpyHostToDevice, c->stream));
+        a.ext_row_lo = c->d_ext_rows + c->pitch;
+    }
+    CU(launch_control(a, c->stream));
+    CU(launch_pass(make_pass_args(c), c->variant, c->stream));
+    c->target_iter += 1;
+    return DPSVM_OK;
+}
+
+int dpsvm_train_async(dpsvm_ctx* c, int iters)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_train_async: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_train_async before dpsvm_upload");
+    if (iters <= 0) return DPSVM_OK;
+    CU(cudaSetDevice(c->device));
+    long long target = (long long)c->target_iter + iters;
+    if (target > INT_MAX) target = INT_MAX;
+    c->target_iter = (int)target;
+    int rc = set_stop_at(c, c->target_iter);
+    if (rc != DPSVM_OK) return rc;
+    const int launches = (iters + c->chunk - 1) / c->chunk;
+    for (int i = 0; i < launches; ++i) {
+        rc = launch_chunk(c);
+        if (rc != DPSVM_OK) return rc;
+    }
+    return DPSVM_OK;
+}
+
+int dpsvm_sync(dpsvm_ctx* c, dpsvm_train_status* status)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_sync: null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(&c->h_st[0], c->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->target_iter = c->h_st[0].num_iter;
+    fill_status(c->h_st[0], 0.f, status);
+    return DPSVM_OK;
+}
+
+void* dpsvm_stream(dpsvm_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int dpsvm_train(dpsvm_ctx* c, int max_new_iter, dpsvm_train_status* status)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_train: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_train before dpsvm_upload");
+    CU(cudaSetDevice(c->device));
+    dpsvm_train_status cur;
+    int rc = dpsvm_sync(c, &cur);
+    if (rc != DPSVM_OK) return rc;
+    long long target = max_new_iter > 0 ? (long long)cur.num_iter + max_new_iter : (long long)INT_MAX;
+    if (target > INT_MAX) target = INT_MAX;
+    rc = set_stop_at(c, (int)target);
+    if (rc != DPSVM_OK) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+
+    // Chunks are launched one ahead of the status read-back so the GPU never waits for the host;
+    // iterations past convergence / the pause point are device-side no-ops.
+    float ms = 0.f;
+    int slot = 0, pending = -1;
+    bool finished = c->h_st[0].done || c->h_st[0].num_iter >= (int)target;
+    while (!finished) {
+        CU(cudaEventRecord(c->ev_t0, c->stream));
+        rc = launch_chunk(c);
+        if (rc != DPSVM_OK) return rc;
+        CU(cudaEventRecord(c->ev_t1, c->stream));
+        CU(cudaMemcpyAsync(&c->h_st[slot], c->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(c->ev_slot[slot], c->stream));
+        if (pending >= 0) {
+            CU(cudaEventSynchronize(c->ev_slot[pending]));
+            const DevState& s = c->h_st[pending];
+            if (s.done || s.num_iter >= (int)target) finished = true;
+        }
+        pending = slot;
+        slot ^= 1;
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    if (pending >= 0) cudaEventElapsedTime(&ms, c->ev_t0, c->ev_t1);
+    CU(cudaMemcpyAsync(&c->h_st[0], c->d_st, sizeof(DevState), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->target_iter = c->h_st[0].num_iter;
+    fill_status(c->h_st[0], ms, status);
+    return DPSVM_OK;
+}
+
+int dpsvm_download(dpsvm_ctx* c, float* h_alpha, float* h_f, float* h_xsq)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_download: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_download before dpsvm_upload");
+    CU(cudaSetDevice(c->device));
+    const int off = c->p.shard_start - c->res0;
+    const size_t n = (size_t)c->p.shard_rows;
+    if (h_alpha) CU(cudaMemcpyAsync(h_alpha, c->d_alpha + off, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+    if (h_f) CU(cudaMemcpyAsync(h_f, c->d_f, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+    if (h_xsq) CU(cudaMemcpyAsync(h_xsq, c->d_xsq + off, sizeof(float) * n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return DPSVM_OK;
+}
+
+int dpsvm_device_state(dpsvm_ctx* c, const float** d_x, int* pitch, const float** d_xsq, const int32_t** d_y,
+                       float** d_alpha, float** d_f)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_device_state: null context");
+    const int off = c->p.shard_start - c->res0;
+    if (d_x) *d_x = c->d_x + (size_t)off * c->pitch;
+    if (pitch) *pitch = c->pitch;
+    if (d_xsq) *d_xsq = c->d_xsq + off;
+    if (d_y) *d_y = c->d_y + off;
+    if (d_alpha) *d_alpha = c->d_alpha + off;
+    if (d_f) *d_f = c->d_f;
+    return DPSVM_OK;
+}
+
+int dpsvm_cache_lookup(dpsvm_ctx* c, int key, float** d_line, int* hit)
+{
+    if (!c || !d_line || !hit) return fail(DPSVM_ERR_INVALID, "dpsvm_cache_lookup: null argument");
+    if (c->cache.lines <= 0) return fail(DPSVM_ERR_STATE, "dpsvm_cache_lookup: cache disabled (cache_size < 2)");
+    if (key < 0 || key >= c->p.num_train_data) return fail(DPSVM_ERR_INVALID, "dpsvm_cache_lookup: key out of range");
+    CU(cudaSetDevice(c->device));
+    int line = -1;
+    int rc = cache_lookup_host(c, key, &line, hit);
+    if (rc != DPSVM_OK) return rc;
+    *d_line = c->cache.data + (size_t)line * c->cache.line_stride;
+    return DPSVM_OK;
+}
+
+}  // extern "C"

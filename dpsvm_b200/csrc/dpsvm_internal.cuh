@@ -1,0 +1,61 @@
+// dpsvm_internal.cuh -- the context structure shared by the library's translation units (internal).
+#pragma once
+
+#include "smo_kernels.cuh"
+
+struct dpsvm_ctx {
+    dpsvm_params p{};
+    int device = 0;
+    int pitch = 0;               // floats per row, multiple of 4
+    int res0 = 0, res_n = 0;     // global row range resident on this GPU (X, xsq, y, alpha)
+    int chunk = 128;             // SMO iterations per CUDA-graph launch
+    int variant = 0;             // pass kernel variant (DPSVM_VARIANT)
+    bool uploaded = false;
+    int target_iter = 0;         // host view of how many iterations have been requested so far
+    int stop_at = 0;
+
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+    cudaEvent_t ev_slot[2] = {nullptr, nullptr};
+
+    float* d_x = nullptr;        // [res_n x pitch]
+    float* d_xsq = nullptr;      // [res_n]
+    int* d_y = nullptr;          // [res_n]
+    float* d_alpha = nullptr;    // [res_n]
+    float* d_f = nullptr;        // [shard_rows]
+    float* d_sel_rows = nullptr; // [2 x pitch] rows of the current pair, read by the pass
+    float* d_ext_rows = nullptr; // [2 x pitch] rows supplied by the host (step2)
+    unsigned long long* d_keys = nullptr;   // [2]
+    dpsvm::DevState* d_st = nullptr;
+    dpsvm::DevState* h_st = nullptr;        // pinned, 2 slots
+    unsigned long long* h_keys = nullptr;   // pinned
+    int* h_small = nullptr;                 // pinned scratch
+
+    dpsvm::CacheDev cache{};
+
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+
+    // multi-GPU
+    int rank = 0, world = 1;
+    void* comm = nullptr;        // opaque (comm.cu)
+
+    // predict scratch (predict.cu)
+    void* predict = nullptr;
+};
+
+namespace dpsvm {
+
+int fail(int code, const char* fmt, ...);
+PassDev make_pass_args(dpsvm_ctx* c);
+CtlDev make_ctl_args(dpsvm_ctx* c);
+
+// cache_host.cu
+int cache_lookup_host(dpsvm_ctx* c, int key, int* line, int* hit);
+// predict.cu
+void predict_free(dpsvm_ctx* c);
+// comm.cu
+void comm_free(dpsvm_ctx* c);
+int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s);
+
+}  // namespace dpsvm

@@ -1,0 +1,680 @@
+// smo_kernels.cu -- hand-written sm_100a kernels of the SMO hot path and their launchers.
+//
+// Kernels (reference call sites they replace, paths in farshid83/dpsvm):
+//   row_norms_kernel     svmTrain.cu:357-364   N x thrust::inner_product in a host loop
+//   init_state_kernel    svmTrain.cu:349,379-380
+//   select_kernel        svmTrain.cu:469-476   for_each(arbitrary_functor) + reduce(my_maxmin)
+//   smo_pass_kernel      svmTrain.cu:222,247 (2 x cublasSgemv) + :276-278 (update_functor) +
+//                        the next iteration's :469-476, fused into ONE sweep over the X shard
+//   smo_control_kernel   svmTrainMain.cpp:246-302 (host merge, eta, alpha update, clip) +
+//                        svmTrain.cu:142-156,487-494 / cache.cu:62-105 (cache lookup, alpha install)
+//
+// The pass is HBM-bound (2 dot products per row = GEMM with N=2, ~1 flop/byte): no tensor cores.
+#include "smo_kernels.cuh"
+
+#include <math.h>
+
+namespace dpsvm {
+
+// ------------------------------------------------------------------------------------------------
+// small PTX helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_stream4(const float4* p)
+{
+    // X is read exactly once per pass: keep it out of L1.
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared (1-D, no tensor map): bytes % 16 == 0, both sides 16 B aligned.
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long umin64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
+
+// Stage the two selected rows in shared memory with TMA bulk copies and zero the tail up to `cap4`.
+__device__ __forceinline__ void stage_selected_rows(float4* s_hi, float4* s_lo, const float4* g_hi, const float4* g_lo,
+                                                    int pitch4, int cap4, uint64_t* bar)
+{
+    const int tid = threadIdx.x;
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t bytes = (uint32_t)pitch4 * 16u;
+        mbar_expect_tx(bar, 2u * bytes);
+        tma_bulk_g2s(s_hi, g_hi, bytes, bar);
+        tma_bulk_g2s(s_lo, g_lo, bytes, bar);
+    }
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = pitch4 + tid; i < cap4; i += blockDim.x) { s_hi[i] = z; s_lo[i] = z; }
+    mbar_wait(bar, 0);
+    __syncthreads();
+}
+
+// Reduce the per-thread best keys over the block and publish with one atomicMin per key.
+__device__ __forceinline__ void publish_keys(unsigned long long best_up, unsigned long long best_low,
+                                             unsigned long long* keys, unsigned long long* s_red)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        best_up = umin64(best_up, __shfl_xor_sync(0xffffffffu, best_up, off));
+        best_low = umin64(best_low, __shfl_xor_sync(0xffffffffu, best_low, off));
+    }
+    if (lane == 0) { s_red[warp] = best_up; s_red[nwarps + warp] = best_low; }
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long u = lane < nwarps ? s_red[lane] : DPSVM_KEY_EMPTY;
+        unsigned long long l = lane < nwarps ? s_red[nwarps + lane] : DPSVM_KEY_EMPTY;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            u = umin64(u, __shfl_xor_sync(0xffffffffu, u, off));
+            l = umin64(l, __shfl_xor_sync(0xffffffffu, l, off));
+        }
+        if (lane == 0) {
+            if (u != DPSVM_KEY_EMPTY) atomicMin(&keys[0], u);
+            if (l != DPSVM_KEY_EMPTY) atomicMin(&keys[1], l);
+        }
+    }
+}
+
+// The per-row tail shared by every pass variant: kernel values, f update (update_functor,
+// svmTrain.cu:128-135), optional cache-line store, classification (arbitrary_functor, :53-91) and
+// the running packed-key minima.
+__device__ __forceinline__ void row_epilogue(int row, float dot_hi, float dot_lo, float xsq_j, float f_j,
+                                             float alpha_j, int y_j, const PassScalars& sc, const PassDev& a,
+                                             bool store_lines, unsigned long long& best_up, unsigned long long& best_low)
+{
+    if (store_lines) {
+        if (sc.line_hi) sc.line_hi[row] = dot_hi;
+        if (sc.line_lo) sc.line_lo[row] = dot_lo;
+    }
+    // expf(-1 * gamma * (xsq_j + x_sel_sq - (2*dot)))      svmTrain.cu:128,130
+    const float arg_hi = __fsub_rn(__fadd_rn(xsq_j, sc.xsq_hi), __fmul_rn(2.0f, dot_hi));
+    const float arg_lo = __fsub_rn(__fadd_rn(xsq_j, sc.xsq_lo), __fmul_rn(2.0f, dot_lo));
+    const float rbf_hi = expf(__fmul_rn(-a.gamma, arg_hi));
+    const float rbf_lo = expf(__fmul_rn(-a.gamma, arg_lo));
+    // delta = (d_alpha_hi*y_hi*rbf_hi) + (d_alpha_lo*y_lo*rbf_lo);  f += delta       svmTrain.cu:133-135
+    const float delta = __fadd_rn(__fmul_rn(sc.delta_hi, rbf_hi), __fmul_rn(sc.delta_lo, rbf_lo));
+    const float f_new = __fadd_rn(f_j, delta);
+    a.f[row] = f_new;
+    bool up, low;
+    iset_membership(alpha_j, y_j, a.c, up, low);
+    const int gidx = a.index_base + row;
+    if (up) best_up = umin64(best_up, pack_key_up(f_new, gidx));
+    if (low) best_low = umin64(best_low, pack_key_low(f_new, gidx));
+}
+
+// Cache fast path: both dot-product lines are resident, X is not touched (28 B per row).
+__device__ __forceinline__ void pass_both_hit(const PassScalars& sc, const PassDev& a,
+                                              unsigned long long& best_up, unsigned long long& best_low)
+{
+    for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += gridDim.x * blockDim.x) {
+        const float dh = sc.line_hi[row], dl = sc.line_lo[row];
+        row_epilogue(row, dh, dl, __ldg(a.xsq + row), a.f[row], __ldg(a.alpha + row), __ldg(a.y + row), sc, a,
+                     false, best_up, best_low);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused pass, variant 0: direct 128-bit streaming loads of X, selected rows staged in smem by TMA.
+//   LPR lanes cooperate on one row, ITERS float4 chunks per lane, R rows in flight per lane group.
+// ------------------------------------------------------------------------------------------------
+template <int LPR, int ITERS>
+__global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev a)
+{
+    constexpr int R = kRowsInFlight;
+    constexpr int GROUPS = 32 / LPR;
+    constexpr int RPW = GROUPS * R;
+    constexpr int CAP4 = LPR * ITERS;
+    static_assert(LPR >= R, "epilogue owners are lanes sub < R");
+
+    __shared__ __align__(16) float4 s_hi[CAP4];
+    __shared__ __align__(16) float4 s_lo[CAP4];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
+
+    const PassScalars sc = a.dev ? *a.dev : a.imm;
+    if (!sc.active) return;
+
+    unsigned long long best_up = DPSVM_KEY_EMPTY, best_low = DPSVM_KEY_EMPTY;
+    if (sc.both_hit) {
+        pass_both_hit(sc, a, best_up, best_low);
+        publish_keys(best_up, best_low, a.keys, s_red);
+        return;
+    }
+
+    stage_selected_rows(s_hi, s_lo, a.x_hi4, a.x_lo4, a.pitch4, CAP4, &s_bar);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % LPR, grp = lane / LPR;
+    const int n_units = (a.n + RPW - 1) / RPW;
+    const int unit_stride = gridDim.x * (kPassThreads / 32);
+
+    for (int unit = blockIdx.x * (kPassThreads / 32) + warp; unit < n_units; unit += unit_stride) {
+        const int row0 = unit * RPW + grp * R;
+        // the lane that will run the epilogue of row (row0 + sub) fetches its scalars up front
+        const int erow = row0 + sub;
+        const bool eown = (sub < R) && (erow < a.n);
+        float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
+        int e_y = 0;
+        if (eown) {
+            e_xsq = __ldg(a.xsq + erow);
+            e_f = a.f[erow];
+            e_alpha = __ldg(a.alpha + erow);
+            e_y = __ldg(a.y + erow);
+        }
+        float4 xv[R][ITERS];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float4* rowp = a.x4 + (size_t)(row0 + r) * a.pitch4;
+            const bool row_ok = (row0 + r) < a.n;
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int c4 = sub + it * LPR;
+                xv[r][it] = (row_ok && c4 < a.pitch4) ? ldg_stream4(rowp + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        float acc_hi[R], acc_lo[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { acc_hi[r] = 0.f; acc_lo[r] = 0.f; }
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it) {
+            const float4 h = s_hi[sub + it * LPR];
+            const float4 l = s_lo[sub + it * LPR];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float4 v = xv[r][it];
+                acc_hi[r] = __fmaf_rn(v.x, h.x, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.x, l.x, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.y, h.y, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.y, l.y, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.z, h.z, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.z, l.z, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.w, h.w, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.w, l.w, acc_lo[r]);
+            }
+        }
+#pragma unroll
+        for (int off = LPR / 2; off >= 1; off >>= 1) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                acc_hi[r] = __fadd_rn(acc_hi[r], __shfl_xor_sync(0xffffffffu, acc_hi[r], off));
+                acc_lo[r] = __fadd_rn(acc_lo[r], __shfl_xor_sync(0xffffffffu, acc_lo[r], off));
+            }
+        }
+        if (eown) {
+            float dh = acc_hi[0], dl = acc_lo[0];
+#pragma unroll
+            for (int r = 1; r < R; ++r) if (sub == r) { dh = acc_hi[r]; dl = acc_lo[r]; }
+            row_epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, sc, a, true, best_up, best_low);
+        }
+    }
+    publish_keys(best_up, best_low, a.keys, s_red);
+}
+
+// Same algorithm for rows too long for the unrolled variants (pitch4 > 256): runtime chunk loop.
+__global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const PassDev a)
+{
+    constexpr int R = kRowsInFlight;
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
+    const int cap4 = ((a.pitch4 + 31) / 32) * 32;
+    float4* s_hi = reinterpret_cast<float4*>(dyn_smem);
+    float4* s_lo = s_hi + cap4;
+
+    const PassScalars sc = a.dev ? *a.dev : a.imm;
+    if (!sc.active) return;
+    unsigned long long best_up = DPSVM_KEY_EMPTY, best_low = DPSVM_KEY_EMPTY;
+    if (sc.both_hit) {
+        pass_both_hit(sc, a, best_up, best_low);
+        publish_keys(best_up, best_low, a.keys, s_red);
+        return;
+    }
+    stage_selected_rows(s_hi, s_lo, a.x_hi4, a.x_lo4, a.pitch4, cap4, &s_bar);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_units = (a.n + R - 1) / R;
+    const int unit_stride = gridDim.x * (kPassThreads / 32);
+    const int iters = cap4 / 32;
+    for (int unit = blockIdx.x * (kPassThreads / 32) + warp; unit < n_units; unit += unit_stride) {
+        const int row0 = unit * R;
+        float acc_hi[R], acc_lo[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) { acc_hi[r] = 0.f; acc_lo[r] = 0.f; }
+        for (int it = 0; it < iters; ++it) {
+            const int c4 = lane + it * 32;
+            const float4 h = s_hi[c4], l = s_lo[c4];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const bool ok = (row0 + r) < a.n && c4 < a.pitch4;
+                const float4 v = ok ? ldg_stream4(a.x4 + (size_t)(row0 + r) * a.pitch4 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                acc_hi[r] = __fmaf_rn(v.x, h.x, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.x, l.x, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.y, h.y, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.y, l.y, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.z, h.z, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.z, l.z, acc_lo[r]);
+                acc_hi[r] = __fmaf_rn(v.w, h.w, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.w, l.w, acc_lo[r]);
+            }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                acc_hi[r] = __fadd_rn(acc_hi[r], __shfl_xor_sync(0xffffffffu, acc_hi[r], off));
+                acc_lo[r] = __fadd_rn(acc_lo[r], __shfl_xor_sync(0xffffffffu, acc_lo[r], off));
+            }
+        }
+        const int erow = row0 + lane;
+        if (lane < R && erow < a.n) {
+            float dh = acc_hi[0], dl = acc_lo[0];
+#pragma unroll
+            for (int r = 1; r < R; ++r) if (lane == r) { dh = acc_hi[r]; dl = acc_lo[r]; }
+            row_epilogue(erow, dh, dl, __ldg(a.xsq + erow), a.f[erow], __ldg(a.alpha + erow), __ldg(a.y + erow), sc, a,
+                         true, best_up, best_low);
+        }
+    }
+    publish_keys(best_up, best_low, a.keys, s_red);
+}
+
+// ------------------------------------------------------------------------------------------------
+// |x_i|^2 with the pass's accumulation order.
+// ------------------------------------------------------------------------------------------------
+template <int LPR, int ITERS>
+__global__ void __launch_bounds__(256) row_norms_kernel(const float4* __restrict__ x4, int n, int pitch4, float* __restrict__ out)
+{
+    constexpr int GROUPS = 32 / LPR;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % LPR, grp = lane / LPR;
+    const int n_units = (n + GROUPS - 1) / GROUPS;
+    for (int unit = blockIdx.x * (blockDim.x >> 5) + warp; unit < n_units; unit += gridDim.x * (blockDim.x >> 5)) {
+        const int row = unit * GROUPS + grp;
+        float acc = 0.f;
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it) {
+            const int c4 = sub + it * LPR;
+            const float4 v = (row < n && c4 < pitch4) ? ldg_stream4(x4 + (size_t)row * pitch4 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            acc = __fmaf_rn(v.x, v.x, acc); acc = __fmaf_rn(v.y, v.y, acc);
+            acc = __fmaf_rn(v.z, v.z, acc); acc = __fmaf_rn(v.w, v.w, acc);
+        }
+#pragma unroll
+        for (int off = LPR / 2; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
+        if (sub == 0 && row < n) out[row] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(256) row_norms_generic_kernel(const float4* __restrict__ x4, int n, int pitch4, float* __restrict__ out)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int iters = (pitch4 + 31) / 32;
+    for (int row = blockIdx.x * (blockDim.x >> 5) + warp; row < n; row += gridDim.x * (blockDim.x >> 5)) {
+        float acc = 0.f;
+        for (int it = 0; it < iters; ++it) {
+            const int c4 = lane + it * 32;
+            const float4 v = c4 < pitch4 ? ldg_stream4(x4 + (size_t)row * pitch4 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            acc = __fmaf_rn(v.x, v.x, acc); acc = __fmaf_rn(v.y, v.y, acc);
+            acc = __fmaf_rn(v.z, v.z, acc); acc = __fmaf_rn(v.w, v.w, acc);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
+        if (lane == 0) out[row] = acc;
+    }
+}
+
+// alpha = 0, f = -y   (svmTrain.cu:349, 379-380)
+__global__ void init_state_kernel(const int* __restrict__ y, int n, float* __restrict__ alpha, float* __restrict__ f)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (alpha) alpha[i] = 0.f;
+        f[i] = -(float)y[i];
+    }
+}
+
+__global__ void __launch_bounds__(256) select_kernel(const float* __restrict__ alpha, const int* __restrict__ y,
+                                                     const float* __restrict__ f, int n, float c, int index_base,
+                                                     unsigned long long* keys)
+{
+    __shared__ unsigned long long s_red[2 * 8];
+    unsigned long long best_up = DPSVM_KEY_EMPTY, best_low = DPSVM_KEY_EMPTY;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        bool up, low;
+        iset_membership(alpha[i], y[i], c, up, low);
+        const float fi = f[i];
+        if (up) best_up = umin64(best_up, pack_key_up(fi, index_base + i));
+        if (low) best_low = umin64(best_low, pack_key_low(fi, index_base + i));
+    }
+    publish_keys(best_up, best_low, keys, s_red);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel-row cache bookkeeping (device-resident LRU; replaces myCache, cache.cu:49-105).
+// Single-thread code: called by thread 0 of the control kernel.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void lru_unlink(const CacheDev& c, int line)
+{
+    const int p = c.prev[line], nx = c.next[line];
+    if (p >= 0) c.next[p] = nx; else c.meta[kCacheHead] = nx;
+    if (nx >= 0) c.prev[nx] = p; else c.meta[kCacheTail] = p;
+}
+__device__ __forceinline__ void lru_append(const CacheDev& c, int line)
+{
+    const int t = c.meta[kCacheTail];
+    c.prev[line] = t; c.next[line] = -1;
+    if (t >= 0) c.next[t] = line; else c.meta[kCacheHead] = line;
+    c.meta[kCacheTail] = line;
+}
+// myCache::lookup (cache.cu:62-80) then, on a miss, myCache::get_new_cache_line (:82-105).
+__device__ int cache_lookup_device(const CacheDev& c, int key, int* hit)
+{
+    int line = c.line_of_key[key];
+    if (line >= 0) {
+        if (c.meta[kCacheTail] != line) { lru_unlink(c, line); lru_append(c, line); }
+        *hit = 1;
+        return line;
+    }
+    *hit = 0;
+    const int size = c.meta[kCacheSize];
+    if (size < c.lines) {
+        line = size;
+        c.meta[kCacheSize] = size + 1;
+    } else {
+        line = c.meta[kCacheHead];            // least recently used
+        c.line_of_key[c.key_of_line[line]] = -1;
+        lru_unlink(c, line);
+    }
+    c.key_of_line[line] = key;
+    c.line_of_key[key] = line;
+    lru_append(c, line);
+    return line;
+}
+
+// Host-callable lookup (SvmTrain::lookup_cache, svmTrain.cu:142-156): out[0] = line, out[1] = hit.
+__global__ void cache_lookup_kernel(const CacheDev c, int key, int* out)
+{
+    int hit = 0;
+    const int line = cache_lookup_device(c, key, &hit);
+    out[0] = line; out[1] = hit;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Control step: one block.  Everything svmTrainMain.cpp:246-308 does on the host between
+// train_step1 and train_step2, plus train_step2's alpha install and cache lookups -- on the device.
+// directed != 0: the pair and the new alphas come from the host (SvmTrain::train_step2 drop-in).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDev a)
+{
+    __shared__ float s_part[kCtlThreads / 32];
+    __shared__ int s_go;
+    const int tid = threadIdx.x;
+    DevState* st = a.st;
+
+    if (tid == 0) {
+        int go = 1;
+        if (!a.directed && (st->done || st->num_iter >= st->stop_at)) go = 0;
+        if (!go) st->pass.active = 0;
+        s_go = go;
+    }
+    __syncthreads();
+    if (!s_go) return;
+
+    int i_hi, i_lo;
+    float b_hi, b_lo;
+    if (a.directed) {
+        i_hi = a.dir_i_hi; i_lo = a.dir_i_lo; b_hi = 0.f; b_lo = 0.f;
+    } else {
+        unpack_key_up(a.keys[0], &b_hi, &i_hi);
+        unpack_key_low(a.keys[1], &b_lo, &i_lo);
+    }
+    const float* src_hi = a.ext_row_hi ? a.ext_row_hi : a.x + (size_t)(i_hi - a.res0) * a.pitch;
+    const float* src_lo = a.ext_row_lo ? a.ext_row_lo : a.x + (size_t)(i_lo - a.res0) * a.pitch;
+
+    // copy the two rows to the staging buffer the pass reads, and |x_hi - x_lo|^2 on the way
+    // (the host kernel of svmTrain.cu:696-714: saxpy(-1) then sdot of the difference).
+    float part = 0.f;
+    for (int i = tid; i < a.pitch; i += kCtlThreads) {
+        const float h = src_hi[i], l = src_lo[i];
+        a.sel_rows[i] = h;
+        a.sel_rows[a.pitch + i] = l;
+        const float df = __fsub_rn(h, l);
+        part = __fmaf_rn(df, df, part);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) part = __fadd_rn(part, __shfl_xor_sync(0xffffffffu, part, off));
+    if ((tid & 31) == 0) s_part[tid >> 5] = part;
+    __syncthreads();
+    if (tid != 0) return;
+
+    float norm_sq = 0.f;
+#pragma unroll
+    for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);
+
+    const int y_hi = a.y[i_hi - a.res0], y_lo = a.y[i_lo - a.res0];
+    const float a_hi_old = a.alpha[i_hi - a.res0], a_lo_old = a.alpha[i_lo - a.res0];
+    float a_hi_new, a_lo_new, eta = 0.f;
+    if (a.directed) {
+        a_hi_new = a.dir_a_hi; a_lo_new = a.dir_a_lo;
+    } else {
+        // eta = K(hi,hi) + K(lo,lo) - 2 K(lo,hi)  (svmTrainMain.cpp:282); K(i,i) = exp(-gamma*0) = 1.
+        // K = (float)exp(-1 * (float)gamma * norm_sq): float product, double exp (svmTrain.cu:709).
+        const float k_lh = (float)exp((double)__fmul_rn(-a.gamma, norm_sq));
+        eta = __fsub_rn(__fadd_rn(1.0f, 1.0f), __fmul_rn(2.0f, k_lh));
+        // svmTrainMain.cpp:289-295; IEEE division (eta == 0 gives +-inf, clipped to 0 or C)
+        const float s = (float)(y_lo * y_hi);
+        const float a_lo_unc = __fadd_rn(a_lo_old, __fdiv_rn(__fmul_rn((float)y_lo, __fsub_rn(b_hi, b_lo)), eta));
+        const float a_hi_unc = __fadd_rn(a_hi_old, __fmul_rn(s, __fsub_rn(a_lo_old, a_lo_unc)));
+        a_lo_new = a_lo_unc < 0.0f ? 0.0f : (a_lo_unc > a.c ? a.c : a_lo_unc);
+        a_hi_new = a_hi_unc < 0.0f ? 0.0f : (a_hi_unc > a.c ? a.c : a_hi_unc);
+    }
+    // alpha[max_idx] = alpha_lo_new; alpha[min_idx] = alpha_hi_new   (svmTrainMain.cpp:298-299)
+    a.alpha[i_lo - a.res0] = a_lo_new;
+    a.alpha[i_hi - a.res0] = a_hi_new;
+
+    PassScalars ps;
+    ps.active = 1;
+    ps.delta_hi = __fmul_rn(__fsub_rn(a_hi_new, a_hi_old), (float)y_hi);
+    ps.delta_lo = __fmul_rn(__fsub_rn(a_lo_new, a_lo_old), (float)y_lo);
+    ps.xsq_hi = a.xsq[i_hi - a.res0];
+    ps.xsq_lo = a.xsq[i_lo - a.res0];
+    ps.line_hi = nullptr; ps.line_lo = nullptr; ps.both_hit = 0;
+    if (a.cache.lines > 0) {
+        // lookup order hi then lo (svmTrain.cu:203,238)
+        int hit_hi, hit_lo;
+        const int l_hi = cache_lookup_device(a.cache, i_hi, &hit_hi);
+        const int l_lo = cache_lookup_device(a.cache, i_lo, &hit_lo);
+        st->cache_lookups += 2;
+        st->cache_hits += hit_hi + hit_lo;
+        float* p_hi = a.cache.data + (size_t)l_hi * a.cache.line_stride;
+        float* p_lo = a.cache.data + (size_t)l_lo * a.cache.line_stride;
+        if (hit_hi && hit_lo) { ps.both_hit = 1; ps.line_hi = p_hi; ps.line_lo = p_lo; }
+        else { if (!hit_hi) ps.line_hi = p_hi; if (!hit_lo && l_lo != l_hi) ps.line_lo = p_lo; }
+    }
+    st->pass = ps;
+    st->i_hi = i_hi; st->i_lo = i_lo; st->eta = eta;
+    const int it = st->num_iter + 1;
+    st->num_iter = it;
+    if (!a.directed) {
+        st->b_hi = b_hi; st->b_lo = b_lo;
+        // while (b_lo > b_hi + 2*epsilon && num_iter < max_iter)   (svmTrainMain.cpp:310)
+        const bool keep_going = b_lo > __fadd_rn(b_hi, __fmul_rn(2.0f, a.epsilon));
+        if (!keep_going) { st->converged = 1; st->done = 1; }
+        if (it >= a.max_iter) st->done = 1;
+    }
+    a.keys[0] = DPSVM_KEY_EMPTY;
+    a.keys[1] = DPSVM_KEY_EMPTY;
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+static int g_num_sms = 0;
+int device_sm_count()
+{
+    if (g_num_sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
+        g_num_sms = v;
+    }
+    return g_num_sms;
+}
+
+template <int LPR, int ITERS>
+static cudaError_t launch_pass_t(const PassDev& a, cudaStream_t s)
+{
+    constexpr int RPW = (32 / LPR) * kRowsInFlight;
+    const int n_units = (a.n + RPW - 1) / RPW;
+    int blocks = (n_units + (kPassThreads / 32) - 1) / (kPassThreads / 32);
+    const int cap = device_sm_count() * 2;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    smo_pass_kernel<LPR, ITERS><<<blocks, kPassThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+template <int LPR>
+static cudaError_t launch_pass_lpr(int iters, const PassDev& a, cudaStream_t s)
+{
+    switch (iters) {
+        case 1: return launch_pass_t<LPR, 1>(a, s);
+        case 2: return launch_pass_t<LPR, 2>(a, s);
+        case 3: return launch_pass_t<LPR, 3>(a, s);
+        case 4: return launch_pass_t<LPR, 4>(a, s);
+        case 5: return launch_pass_t<LPR, 5>(a, s);
+        case 6: return launch_pass_t<LPR, 6>(a, s);
+        case 7: return launch_pass_t<LPR, 7>(a, s);
+        case 8: return launch_pass_t<LPR, 8>(a, s);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s)
+{
+    (void)variant;
+    if (a.n <= 0) return cudaSuccess;
+    if (a.pitch4 > 256) {
+        const int cap4 = ((a.pitch4 + 31) / 32) * 32;
+        const size_t smem = (size_t)cap4 * 2 * sizeof(float4);
+        if (smem > 200 * 1024) return cudaErrorInvalidValue;
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(smo_pass_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_set = true;
+        }
+        const int n_units = (a.n + kRowsInFlight - 1) / kRowsInFlight;
+        int blocks = (n_units + 7) / 8;
+        const int cap = device_sm_count() * 2;
+        if (blocks > cap) blocks = cap;
+        smo_pass_generic_kernel<<<blocks, kPassThreads, smem, s>>>(a);
+        return cudaGetLastError();
+    }
+    const DotGeom g = dot_geometry(a.pitch4);
+    switch (g.lpr) {
+        case 4: return launch_pass_lpr<4>(g.iters, a, s);
+        case 8: return launch_pass_lpr<8>(g.iters, a, s);
+        case 16: return launch_pass_lpr<16>(g.iters, a, s);
+        default: return launch_pass_lpr<32>(g.iters, a, s);
+    }
+}
+
+template <int LPR>
+static cudaError_t launch_norms_lpr(int iters, const float4* x4, int n, int pitch4, float* out, cudaStream_t s)
+{
+    const int groups = 32 / LPR;
+    const int n_units = (n + groups - 1) / groups;
+    int blocks = (n_units + 7) / 8;
+    const int cap = device_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    switch (iters) {
+        case 1: row_norms_kernel<LPR, 1><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 2: row_norms_kernel<LPR, 2><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 3: row_norms_kernel<LPR, 3><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 4: row_norms_kernel<LPR, 4><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 5: row_norms_kernel<LPR, 5><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 6: row_norms_kernel<LPR, 6><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 7: row_norms_kernel<LPR, 7><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        case 8: row_norms_kernel<LPR, 8><<<blocks, 256, 0, s>>>(x4, n, pitch4, out); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_row_norms(const float* x, int n, int pitch, float* out, cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    const int pitch4 = pitch / 4;
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    if (pitch4 > 256) {
+        int blocks = (n + 7) / 8;
+        const int cap = device_sm_count() * 8;
+        if (blocks > cap) blocks = cap;
+        row_norms_generic_kernel<<<blocks, 256, 0, s>>>(x4, n, pitch4, out);
+        return cudaGetLastError();
+    }
+    const DotGeom g = dot_geometry(pitch4);
+    switch (g.lpr) {
+        case 4: return launch_norms_lpr<4>(g.iters, x4, n, pitch4, out, s);
+        case 8: return launch_norms_lpr<8>(g.iters, x4, n, pitch4, out, s);
+        case 16: return launch_norms_lpr<16>(g.iters, x4, n, pitch4, out, s);
+        default: return launch_norms_lpr<32>(g.iters, x4, n, pitch4, out, s);
+    }
+}
+
+cudaError_t launch_init_state(const int* y, int n, float* alpha, float* f, cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    int blocks = (n + 255) / 256;
+    const int cap = device_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    init_state_kernel<<<blocks, 256, 0, s>>>(y, n, alpha, f);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_select(const float* alpha, const int* y, const float* f, int n, float c, int index_base,
+                          unsigned long long* keys, cudaStream_t s)
+{
+    cudaError_t e = cudaMemsetAsync(keys, 0xFF, 2 * sizeof(unsigned long long), s);
+    if (e != cudaSuccess) return e;
+    if (n <= 0) return cudaSuccess;
+    int blocks = (n + 255) / 256;
+    const int cap = device_sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    select_kernel<<<blocks, 256, 0, s>>>(alpha, y, f, n, c, index_base, keys);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStream_t s)
+{
+    cache_lookup_kernel<<<1, 1, 0, s>>>(c, key, d_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_control(const CtlDev& a, cudaStream_t s)
+{
+    smo_control_kernel<<<1, kCtlThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace dpsvm

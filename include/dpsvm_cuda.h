@@ -198,6 +198,8 @@ typedef struct {
     long long cache_hits;  /* kernel-row cache hits / lookups (2 lookups per iteration) */
     long long cache_lookups;
     float last_chunk_ms;   /* device time of the last graph launch (CUDA events) */
+    int i_hi, i_lo;        /* pair of the last executed iteration (global indices) */
+    float eta;             /* its eta (svmTrainMain.cpp:282) */
 } dpsvm_train_status;
 
 int dpsvm_train(dpsvm_ctx* ctx, int max_new_iter, dpsvm_train_status* status);
