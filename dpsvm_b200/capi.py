@@ -48,6 +48,20 @@ class PassArgs(C.Structure):
                 ("d_keys", C.c_void_p), ("d_line_hi", C.c_void_p), ("d_line_lo", C.c_void_p), ("variant", C.c_int)]
 
 
+class IterationInfo(C.Structure):
+    _fields_ = [("i_hi", C.c_int32), ("i_lo", C.c_int32), ("b_hi", C.c_float), ("b_lo", C.c_float),
+                ("eta", C.c_float), ("converged", C.c_int32)]
+
+
+class IterationArgs(C.Structure):
+    _fields_ = [("d_x", C.c_void_p), ("n", C.c_int), ("d", C.c_int), ("pitch", C.c_int),
+                ("d_xsq", C.c_void_p), ("d_y", C.c_void_p), ("d_alpha", C.c_void_p), ("d_f", C.c_void_p),
+                ("d_keys", C.c_void_p), ("c", C.c_float), ("gamma", C.c_float), ("epsilon", C.c_float),
+                ("index_base", C.c_int), ("d_info", C.c_void_p)]
+
+
+NOALLOC_MAX_PITCH = 4096
+
 # every symbol include/dpsvm_cuda.h declares (tests check the library exports all of them)
 EXPORTS = [
     "dpsvm_last_error", "dpsvm_abi_version", "dpsvm_shard_layout", "dpsvm_merge_candidates", "dpsvm_alpha_update",
@@ -55,7 +69,7 @@ EXPORTS = [
     "dpsvm_row_norms", "dpsvm_init_state", "dpsvm_select", "dpsvm_smo_pass", "dpsvm_create", "dpsvm_destroy",
     "dpsvm_upload", "dpsvm_upload_device", "dpsvm_reset", "dpsvm_step1", "dpsvm_step2", "dpsvm_train",
     "dpsvm_train_async", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
-    "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init",
+    "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init", "dpsvm_smo_iteration_noalloc",
 ]
 
 _lib = None
@@ -81,6 +95,7 @@ def lib():
         L.dpsvm_init_state.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.dpsvm_select.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.dpsvm_smo_pass.argtypes = [C.POINTER(PassArgs), C.c_void_p]
+        L.dpsvm_smo_iteration_noalloc.argtypes = [C.POINTER(IterationArgs), C.c_void_p]
         L.dpsvm_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
         L.dpsvm_destroy.argtypes = [C.c_void_p]
         L.dpsvm_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -193,6 +208,18 @@ def smo_pass(stream=None, **kw):
         else:
             setattr(a, k, v)
     check(lib().dpsvm_smo_pass(C.byref(a), _ptr(stream)))
+
+
+def smo_iteration_noalloc(stream=None, **kw):
+    """One SMO iteration on caller-owned device arrays with no allocation (dpsvm_smo_iteration_noalloc)."""
+    a = IterationArgs()
+    for k, v in kw.items():
+        if k.startswith("d_"):
+            p = _ptr(v)
+            setattr(a, k, p.value if p is not None else None)
+        else:
+            setattr(a, k, v)
+    check(lib().dpsvm_smo_iteration_noalloc(C.byref(a), _ptr(stream)))
 
 
 # ---- trainer context --------------------------------------------------------------------------

@@ -232,6 +232,58 @@ int dpsvm_predict(dpsvm_ctx* ctx, const float* h_alpha_full, const int32_t* h_y_
                   float* h_dual, int32_t* h_pred, int* num_sv, float* accuracy);
 
 /* ------------------------------------------------------------------------------------------------
+ * One SMO iteration that allocates nothing
+ * ---------------------------------------------------------------------------------------------- */
+
+/* This entry point has no counterpart in the reference.
+ *
+ * It exists for callers that cannot call cudaMalloc when they need to advance the solver: a plugin
+ * inside a framework whose own allocator already owns the device, a thread that must not trigger
+ * the device-wide synchronisation cudaMalloc / cudaFree imply, or a program running under a memory
+ * budget that was fixed at start-up.  It runs exactly the two kernels one iteration of dpsvm_train
+ * runs (control step, then the fused pass) on arrays the CALLER owns, and keeps the small work area
+ * those kernels need (the two selected rows and the iteration state) in a fixed array inside the
+ * library image instead of in cudaMalloc'ed memory.  The call itself performs no cudaMalloc,
+ * cudaFree or any other allocating routine.
+ *
+ * Limits and rules
+ *   - pitch <= DPSVM_NOALLOC_MAX_PITCH floats; wider rows are rejected with DPSVM_ERR_LIMIT.  The
+ *     work area is 33 024 bytes per GPU, held by every GPU that loads the library until exit.
+ *   - no kernel-row cache (every iteration recomputes both kernel rows).
+ *   - d_keys must hold the current selection on entry (dpsvm_select, or the previous call's
+ *     output) and receives the next one; d_alpha and d_f are updated in place; all rows referenced
+ *     by the keys must lie in [index_base, index_base + n).
+ *   - the first call on each device also looks up the work area's device address; make that first
+ *     call before starting any stream capture on that device.
+ *   - every call on a device shares the one work area, which keeps the previous call's contents
+ *     (the call clears what it needs cleared).  Two calls that overlap on the GPU -- different
+ *     streams, or different host threads -- race on it; serialise them on one stream.
+ *   - asynchronous on `stream`; outputs are valid once the stream has drained.  */
+#define DPSVM_NOALLOC_MAX_PITCH 4096
+
+typedef struct {
+    int32_t i_hi, i_lo;      /* the pair this iteration worked on (global indices) */
+    float b_hi, b_lo;        /* svmTrainMain.cpp:276-277 */
+    float eta;               /* svmTrainMain.cpp:282 */
+    int32_t converged;       /* 1 if b_lo <= b_hi + 2*epsilon was observed (the update is still applied) */
+} dpsvm_iteration_info;
+
+typedef struct {
+    const float* d_x;        /* [n x pitch] rows, zero padded */
+    int n, d, pitch;
+    const float* d_xsq;      /* [n] from dpsvm_row_norms */
+    const int32_t* d_y;      /* [n] */
+    float* d_alpha;          /* [n] in/out */
+    float* d_f;              /* [n] in/out */
+    uint64_t* d_keys;        /* [2] in/out */
+    float c, gamma, epsilon;
+    int index_base;          /* global index of row 0 */
+    dpsvm_iteration_info* d_info;   /* optional DEVICE pointer, filled on the stream */
+} dpsvm_iteration_args;
+
+int dpsvm_smo_iteration_noalloc(const dpsvm_iteration_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Multi-GPU (one process per GPU; replaces the OpenMPI Allgather of svmTrainMain.cpp:244)
  * ---------------------------------------------------------------------------------------------- */
 
