@@ -65,7 +65,7 @@ NOALLOC_MAX_PITCH = 4096
 # every symbol include/dpsvm_cuda.h declares (tests check the library exports all of them)
 EXPORTS = [
     "dpsvm_last_error", "dpsvm_abi_version", "dpsvm_shard_layout", "dpsvm_merge_candidates", "dpsvm_alpha_update",
-    "dpsvm_pitch_for", "dpsvm_pack_key_up", "dpsvm_pack_key_low", "dpsvm_unpack_key_up", "dpsvm_unpack_key_low",
+    "dpsvm_pitch_for", "dpsvm_pass_variant", "dpsvm_pack_key_up", "dpsvm_pack_key_low", "dpsvm_unpack_key_up", "dpsvm_unpack_key_low",
     "dpsvm_row_norms", "dpsvm_init_state", "dpsvm_select", "dpsvm_smo_pass", "dpsvm_create", "dpsvm_destroy",
     "dpsvm_upload", "dpsvm_upload_device", "dpsvm_reset", "dpsvm_step1", "dpsvm_step2", "dpsvm_train",
     "dpsvm_train_async", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
@@ -144,6 +144,10 @@ def _ptr(a):
 # ---- host-only helpers -----------------------------------------------------------------------
 def pitch_for(d: int) -> int:
     return lib().dpsvm_pitch_for(d)
+
+
+def pass_variant(n: int, pitch: int, parity: int) -> int:
+    return lib().dpsvm_pass_variant(n, pitch, parity)
 
 
 def shard_layout(n_total: int, world: int):

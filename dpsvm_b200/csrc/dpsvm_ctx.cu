@@ -75,6 +75,9 @@ PassDev make_pass_args(dpsvm_ctx* c)
     a.index_base = c->p.shard_start;
     a.keys = c->d_keys;
     a.dev = &c->d_st->pass;
+    // with a large cache a both-rows-cached iteration (no X sweep) is likely: do not pre-issue X loads
+    a.early_load = c->cache.lines < 64;
+    a.pdl = c->pdl;
     return a;
 }
 
@@ -95,37 +98,64 @@ CtlDev make_ctl_args(dpsvm_ctx* c)
     a.epsilon = c->p.epsilon;
     a.max_iter = c->p.max_iter;
     a.cache = c->cache;
+    a.pdl = c->pdl;
     return a;
 }
 
-static int launch_iteration(dpsvm_ctx* c, cudaStream_t s)
+// Variant word of the pass for iteration `parity` (bit 0 reverse, bit 1 L2 hints, >> 8 pinned MB).
+// Default policy, from profiles/r01_l2_sweep.md: every SMO iteration re-reads the same X, so
+//   * serpentine order -- odd iterations sweep back to front, starting on what L2 still holds;
+//   * a 32 MB prefix of X is loaded evict_last, the rest evict_first, once X is too big for L2.
+static int variant_for(const dpsvm_ctx* c, int parity)
 {
-    if (c->world > 1) return comm_launch_iteration(c, s);
+    return c->variant ^ ((c->serpentine && (parity & 1)) ? 1 : 0);
+}
+
+static int launch_iteration(dpsvm_ctx* c, cudaStream_t s, int parity)
+{
+    if (c->world > 1) return comm_launch_iteration(c, s, variant_for(c, parity));
     CU(launch_control(make_ctl_args(c), s));
-    CU(launch_pass(make_pass_args(c), c->variant, s));
+    CU(launch_pass(make_pass_args(c), variant_for(c, parity), s));
+    return DPSVM_OK;
+}
+
+static int capture_graph(dpsvm_ctx* c)
+{
+    CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = DPSVM_OK;
+    for (int i = 0; i < c->chunk && rc == DPSVM_OK; ++i) rc = launch_iteration(c, c->stream, i);
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+    if (rc != DPSVM_OK) { if (g) cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&c->gexec, g, 0);
+    if (e != cudaSuccess) {
+        cudaGraphDestroy(g);
+        c->gexec = nullptr;
+        return fail(DPSVM_ERR_CUDA, "graph instantiate failed: %s", cudaGetErrorString(e));
+    }
+    c->graph = g;
     return DPSVM_OK;
 }
 
 static int build_graph(dpsvm_ctx* c)
 {
     if (c->gexec) return DPSVM_OK;
-    CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = DPSVM_OK;
-    for (int i = 0; i < c->chunk && rc == DPSVM_OK; ++i) rc = launch_iteration(c, c->stream);
-    cudaGraph_t g = nullptr;
-    cudaError_t e = cudaStreamEndCapture(c->stream, &g);
-    if (rc != DPSVM_OK) { if (g) cudaGraphDestroy(g); return rc; }
-    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
-    c->graph = g;
-    CU(cudaGraphInstantiate(&c->gexec, c->graph, 0));
-    return DPSVM_OK;
+    int rc = capture_graph(c);
+    if (rc != DPSVM_OK && c->pdl) {
+        // programmatic edges not accepted by this driver in a captured graph: plain edges instead
+        cudaGetLastError();
+        c->pdl = 0;
+        rc = capture_graph(c);
+    }
+    return rc;
 }
 
 static int launch_chunk(dpsvm_ctx* c)
 {
     if (c->p.flags & DPSVM_FLAG_NO_GRAPH) {
         for (int i = 0; i < c->chunk; ++i) {
-            int rc = launch_iteration(c, c->stream);
+            int rc = launch_iteration(c, c->stream, i);
             if (rc != DPSVM_OK) return rc;
         }
         return DPSVM_OK;
@@ -244,6 +274,7 @@ int dpsvm_smo_pass(const dpsvm_pass_args* g, void* stream)
     a.imm.xsq_hi = g->xsq_hi; a.imm.xsq_lo = g->xsq_lo;
     a.imm.line_hi = g->d_line_hi; a.imm.line_lo = g->d_line_lo;
     a.dev = nullptr;
+    a.early_load = 1;
     CU(launch_pass(a, g->variant, (cudaStream_t)stream));
     return DPSVM_OK;
 }
@@ -272,7 +303,10 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     c->res_n = shard_only ? p->shard_rows : p->num_train_data;
     c->chunk = env_int("DPSVM_CHUNK", 128);
     if (c->chunk < 1) c->chunk = 1;
-    c->variant = env_int("DPSVM_VARIANT", 0);
+    c->variant = env_int("DPSVM_VARIANT", dpsvm_pass_variant(p->shard_rows, c->pitch, 0));
+    c->serpentine = env_int("DPSVM_SERPENTINE", 1);
+    c->pdl = env_int("DPSVM_PDL", 1);
+    if (c->chunk > 1 && (c->chunk & 1)) c->chunk += 1;   // even chunks keep the direction alternating across launches
     c->world = 1; c->rank = 0;
     // the reference with one line aliases the hi and lo buffers (latent bug, cache.cu:82-105): a
     // single line cannot hold both rows of an iteration, so 1 behaves as "cache off" here.
@@ -412,7 +446,7 @@ int dpsvm_step2(dpsvm_ctx* c, int i_hi, int i_lo, float alpha_hi_new, float alph
         a.ext_row_lo = c->d_ext_rows + c->pitch;
     }
     CU(launch_control(a, c->stream));
-    CU(launch_pass(make_pass_args(c), c->variant, c->stream));
+    CU(launch_pass(make_pass_args(c), variant_for(c, c->target_iter), c->stream));
     c->target_iter += 1;
     return DPSVM_OK;
 }

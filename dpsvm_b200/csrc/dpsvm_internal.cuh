@@ -9,7 +9,9 @@ struct dpsvm_ctx {
     int pitch = 0;               // floats per row, multiple of 4
     int res0 = 0, res_n = 0;     // global row range resident on this GPU (X, xsq, y, alpha)
     int chunk = 128;             // SMO iterations per CUDA-graph launch
-    int variant = 0;             // pass kernel variant (DPSVM_VARIANT)
+    int variant = 0;             // pass kernel variant word (DPSVM_VARIANT): bit0 reverse, bit1 L2 hints, >>8 pinned MB
+    int serpentine = 0;          // alternate the sweep direction between consecutive iterations
+    int pdl = 1;                 // programmatic dependent launch between control and pass kernels
     bool uploaded = false;
     int target_iter = 0;         // host view of how many iterations have been requested so far
     int stop_at = 0;
@@ -56,6 +58,6 @@ int cache_lookup_host(dpsvm_ctx* c, int key, int* line, int* hit);
 void predict_free(dpsvm_ctx* c);
 // comm.cu
 void comm_free(dpsvm_ctx* c);
-int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s);
+int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s, int variant);
 
 }  // namespace dpsvm

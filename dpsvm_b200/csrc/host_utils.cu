@@ -54,6 +54,16 @@ int dpsvm_alpha_update(float eta, int y_hi, int y_lo, float b_hi, float b_lo, fl
 
 int dpsvm_pitch_for(int d) { return d <= 0 ? 0 : (d + 3) / 4 * 4; }
 
+// Default L2 policy of the fused pass for a shard of n rows (see dpsvm_ctx.cu: variant_for).
+int dpsvm_pass_variant(int n, int pitch, int iteration_parity)
+{
+    const double x_mb = 4e-6 * (double)n * (double)pitch;
+    int v = 0;
+    if (x_mb > 64.0) v = 2 | (32 << 8);          // L2 hints, 32 MB pinned prefix
+    if (iteration_parity & 1) v ^= 1;            // serpentine: odd iterations sweep in reverse
+    return v;
+}
+
 uint64_t dpsvm_pack_key_up(float f, int32_t index) { return pack_key_up(f, index); }
 uint64_t dpsvm_pack_key_low(float f, int32_t index) { return pack_key_low(f, index); }
 void dpsvm_unpack_key_up(uint64_t key, float* f, int32_t* index) { unpack_key_up(key, f, index); }

@@ -140,6 +140,7 @@ extern "C" int dpsvm_smo_iteration_noalloc(const dpsvm_iteration_args* g, void* 
     p.index_base = g->index_base;
     p.keys = reinterpret_cast<unsigned long long*>(g->d_keys);
     p.dev = &st->pass;
+    p.early_load = 1;
     e = launch_pass(p, 0, s);
     if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "dpsvm_smo_iteration_noalloc: pass launch -> %s", cudaGetErrorString(e));
 

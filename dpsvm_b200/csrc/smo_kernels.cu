@@ -142,10 +142,29 @@ __device__ __forceinline__ void pass_both_hit(const PassScalars& sc, const PassD
 }
 
 // ------------------------------------------------------------------------------------------------
-// Fused pass, variant 0: direct 128-bit streaming loads of X, selected rows staged in smem by TMA.
+// Fused pass: direct 128-bit streaming loads of X, selected rows staged in smem by TMA.
 //   LPR lanes cooperate on one row, ITERS float4 chunks per lane, R rows in flight per lane group.
+//   HINT: loads carry an L2 eviction-priority policy -- units below a.pin_units are kept
+//   (evict_last), the rest streamed (evict_first) -- so a prefix of X stays L2-resident from one
+//   SMO iteration to the next (every iteration re-reads the same X).
+//   a.reverse: sweep the units back to front (serpentine order across consecutive iterations: the
+//   tail of the previous pass is what L2 still holds).
 // ------------------------------------------------------------------------------------------------
-template <int LPR, int ITERS>
+template <bool HINT>
+__device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
+{
+    float4 v;
+    if (HINT) {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    }
+    return v;
+}
+
+template <int LPR, int ITERS, bool HINT>
 __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev a)
 {
     constexpr int R = kRowsInFlight;
@@ -159,6 +178,65 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
 
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % LPR, grp = lane / LPR;
+    const int n_units = (a.n + RPW - 1) / RPW;
+    const int unit_stride = gridDim.x * (kPassThreads / 32);
+
+    uint64_t pol_keep = 0, pol_stream = 0;
+    if (HINT) {
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+    }
+
+    // per-unit registers
+    float4 xv[R][ITERS];
+    float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
+    int e_y = 0, erow = 0;
+    bool eown = false;
+
+    // constants of the unit (X, |x|^2, y): may be loaded before the dependency wait
+    auto load_unit = [&](int unit) {
+        const int u = a.reverse ? (n_units - 1 - unit) : unit;
+        const int row0 = u * RPW + grp * R;
+        const uint64_t pol = (u < a.pin_units) ? pol_keep : pol_stream;
+        // the lane that will run the epilogue of row (row0 + sub) fetches its scalars up front
+        erow = row0 + sub;
+        eown = (sub < R) && (erow < a.n);
+        if (eown) {
+            e_xsq = __ldg(a.xsq + erow);
+            e_y = __ldg(a.y + erow);
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float4* rowp = a.x4 + (size_t)(row0 + r) * a.pitch4;
+            const bool row_ok = (row0 + r) < a.n;
+#pragma unroll
+            for (int it = 0; it < ITERS; ++it) {
+                const int c4 = sub + it * LPR;
+                xv[r][it] = (row_ok && c4 < a.pitch4) ? ldg_x4<HINT>(rowp + c4, pol) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+    };
+    // state of the unit (f from the previous pass, alpha from the control step): only after the wait
+    auto load_unit_state = [&]() {
+        if (eown) {
+            e_f = a.f[erow];
+            e_alpha = a.alpha[erow];
+        }
+    };
+
+    int unit = blockIdx.x * (kPassThreads / 32) + warp;
+    // X does not depend on the pair: when a both-rows-cached iteration is unlikely (a.early_load),
+    // put the first unit's loads in flight before waiting for anything else.
+    bool loaded = false;
+    if (a.early_load && unit < n_units) { load_unit(unit); loaded = true; }
+
+    // Programmatic dependent launch: let the next kernel in the stream become resident early, then
+    // wait until the previous one (the control step) has completed and its writes are visible.
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
     const PassScalars sc = a.dev ? *a.dev : a.imm;
     if (!sc.active) return;
 
@@ -171,35 +249,10 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev
 
     stage_selected_rows(s_hi, s_lo, a.x_hi4, a.x_lo4, a.pitch4, CAP4, &s_bar);
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int sub = lane % LPR, grp = lane / LPR;
-    const int n_units = (a.n + RPW - 1) / RPW;
-    const int unit_stride = gridDim.x * (kPassThreads / 32);
-
-    for (int unit = blockIdx.x * (kPassThreads / 32) + warp; unit < n_units; unit += unit_stride) {
-        const int row0 = unit * RPW + grp * R;
-        // the lane that will run the epilogue of row (row0 + sub) fetches its scalars up front
-        const int erow = row0 + sub;
-        const bool eown = (sub < R) && (erow < a.n);
-        float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
-        int e_y = 0;
-        if (eown) {
-            e_xsq = __ldg(a.xsq + erow);
-            e_f = a.f[erow];
-            e_alpha = __ldg(a.alpha + erow);
-            e_y = __ldg(a.y + erow);
-        }
-        float4 xv[R][ITERS];
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const float4* rowp = a.x4 + (size_t)(row0 + r) * a.pitch4;
-            const bool row_ok = (row0 + r) < a.n;
-#pragma unroll
-            for (int it = 0; it < ITERS; ++it) {
-                const int c4 = sub + it * LPR;
-                xv[r][it] = (row_ok && c4 < a.pitch4) ? ldg_stream4(rowp + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
+    for (; unit < n_units; unit += unit_stride) {
+        if (!loaded) load_unit(unit);
+        loaded = false;
+        load_unit_state();
         float acc_hi[R], acc_lo[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) { acc_hi[r] = 0.f; acc_lo[r] = 0.f; }
@@ -245,6 +298,8 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
     float4* s_hi = reinterpret_cast<float4*>(dyn_smem);
     float4* s_lo = s_hi + cap4;
 
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const PassScalars sc = a.dev ? *a.dev : a.imm;
     if (!sc.active) return;
     unsigned long long best_up = DPSVM_KEY_EMPTY, best_low = DPSVM_KEY_EMPTY;
@@ -384,9 +439,9 @@ __device__ __forceinline__ void lru_append(const CacheDev& c, int line)
     c.meta[kCacheTail] = line;
 }
 // myCache::lookup (cache.cu:62-80) then, on a miss, myCache::get_new_cache_line (:82-105).
-__device__ int cache_lookup_device(const CacheDev& c, int key, int* hit)
+// `line` is line_of_key[key] as the caller already loaded it (-1 = not cached).
+__device__ int cache_lookup_device(const CacheDev& c, int key, int line, int* hit)
 {
-    int line = c.line_of_key[key];
     if (line >= 0) {
         if (c.meta[kCacheTail] != line) { lru_unlink(c, line); lru_append(c, line); }
         *hit = 1;
@@ -412,7 +467,7 @@ __device__ int cache_lookup_device(const CacheDev& c, int key, int* hit)
 __global__ void cache_lookup_kernel(const CacheDev c, int key, int* out)
 {
     int hit = 0;
-    const int line = cache_lookup_device(c, key, &hit);
+    const int line = cache_lookup_device(c, key, c.line_of_key[key], &hit);
     out[0] = line; out[1] = hit;
 }
 
@@ -420,34 +475,92 @@ __global__ void cache_lookup_kernel(const CacheDev c, int key, int* out)
 // Control step: one block.  Everything svmTrainMain.cpp:246-308 does on the host between
 // train_step1 and train_step2, plus train_step2's alpha install and cache lookups -- on the device.
 // directed != 0: the pair and the new alphas come from the host (SvmTrain::train_step2 drop-in).
+//
+// Built for latency (it sits on the critical path of every iteration):
+//   * launched with programmatic dependent launch: it becomes resident while the previous pass is
+//     still draining and lets the next pass do the same (griddepcontrol);
+//   * every independent global load is issued at once: the two rows by the whole block, the eight
+//     per-row scalars by eight lanes of warp 0, the recency lists of a small cache by the whole
+//     block into shared memory -- so the serial part (eta, alpha update, LRU pointer chasing) runs
+//     on registers and shared memory only.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDev a)
 {
+    extern __shared__ int s_cache[];                  // [3 * lines + kCacheMetaInts] when the cache is staged
     __shared__ float s_part[kCtlThreads / 32];
-    __shared__ int s_go;
+    __shared__ float s_scal[8];
     const int tid = threadIdx.x;
     DevState* st = a.st;
 
-    if (tid == 0) {
-        int go = 1;
-        if (!a.directed && (st->done || st->num_iter >= st->stop_at)) go = 0;
-        if (!go) st->pass.active = 0;
-        s_go = go;
-    }
-    __syncthreads();
-    if (!s_go) return;
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
+    // uniform loads (one transaction per warp, no barrier needed to share them)
+    const int done = st->done, num_iter = st->num_iter, stop_at = st->stop_at;
+    const unsigned long long k_up = a.keys[0], k_low = a.keys[1];
+    if (!a.directed && (done || num_iter >= stop_at)) {
+        if (tid == 0) st->pass.active = 0;
+        return;
+    }
     int i_hi, i_lo;
     float b_hi, b_lo;
+    const CandHeader* h_hi = nullptr;
+    const CandHeader* h_lo = nullptr;
     if (a.directed) {
         i_hi = a.dir_i_hi; i_lo = a.dir_i_lo; b_hi = 0.f; b_lo = 0.f;
+    } else if (a.world > 1) {
+        // Global merge of the gathered packages (svmTrainMain.cpp:255-274): the minimum packed key is
+        // argmin f / argmax f with the lowest GLOBAL index among equal values, identical on every rank.
+        unsigned long long g_up = DPSVM_KEY_EMPTY, g_low = DPSVM_KEY_EMPTY;
+        int w_up = 0, w_low = 0;
+        for (int r = 0; r < a.world; ++r) {
+            const CandHeader* h = reinterpret_cast<const CandHeader*>(a.cand + (size_t)r * a.cand_stride);
+            const unsigned long long u = h->key_up, l = h->key_low;
+            if (u < g_up) { g_up = u; w_up = r; }
+            if (l < g_low) { g_low = l; w_low = r; }
+        }
+        unpack_key_up(g_up, &b_hi, &i_hi);
+        unpack_key_low(g_low, &b_lo, &i_lo);
+        h_hi = reinterpret_cast<const CandHeader*>(a.cand + (size_t)w_up * a.cand_stride);
+        h_lo = reinterpret_cast<const CandHeader*>(a.cand + (size_t)w_low * a.cand_stride);
     } else {
-        unpack_key_up(a.keys[0], &b_hi, &i_hi);
-        unpack_key_low(a.keys[1], &b_lo, &i_lo);
+        unpack_key_up(k_up, &b_hi, &i_hi);
+        unpack_key_low(k_low, &b_lo, &i_lo);
     }
-    const float* src_hi = a.ext_row_hi ? a.ext_row_hi : a.x + (size_t)(i_hi - a.res0) * a.pitch;
-    const float* src_lo = a.ext_row_lo ? a.ext_row_lo : a.x + (size_t)(i_lo - a.res0) * a.pitch;
+    const int r_hi = i_hi - a.res0, r_lo = i_lo - a.res0;
+    const float* src_hi = a.ext_row_hi ? a.ext_row_hi : a.x + (size_t)r_hi * a.pitch;
+    const float* src_lo = a.ext_row_lo ? a.ext_row_lo : a.x + (size_t)r_lo * a.pitch;
+    if (h_hi) {
+        src_hi = reinterpret_cast<const float*>(h_hi + 1);                 // package: header, row_hi, row_lo
+        src_lo = reinterpret_cast<const float*>(h_lo + 1) + a.pitch;
+    }
+    const bool cache_on = a.cache.lines > 0;
+    const bool staged = cache_on && a.cache.lines <= kCacheSmemLines;
 
+    // ---- everything that can be loaded now, in one round ----
+    if (tid < 8) {
+        float v;
+        switch (tid) {
+            case 0: v = h_hi ? (float)h_hi->y_hi : (float)a.y[r_hi]; break;
+            case 1: v = h_lo ? (float)h_lo->y_lo : (float)a.y[r_lo]; break;
+            case 2: v = h_hi ? h_hi->a_hi : a.alpha[r_hi]; break;
+            case 3: v = h_lo ? h_lo->a_lo : a.alpha[r_lo]; break;
+            case 4: v = h_hi ? h_hi->xsq_hi : a.xsq[r_hi]; break;
+            case 5: v = h_lo ? h_lo->xsq_lo : a.xsq[r_lo]; break;
+            case 6: v = cache_on ? __int_as_float(a.cache.line_of_key[i_hi]) : 0.f; break;
+            default: v = cache_on ? __int_as_float(a.cache.line_of_key[i_lo]) : 0.f; break;
+        }
+        s_scal[tid] = v;
+    }
+    if (staged) {
+        const int L = a.cache.lines;
+        for (int i = tid; i < L; i += kCtlThreads) {
+            s_cache[i] = a.cache.key_of_line[i];
+            s_cache[L + i] = a.cache.prev[i];
+            s_cache[2 * L + i] = a.cache.next[i];
+        }
+        if (tid < kCacheMetaInts) s_cache[3 * L + tid] = a.cache.meta[tid];
+    }
     // copy the two rows to the staging buffer the pass reads, and |x_hi - x_lo|^2 on the way
     // (the host kernel of svmTrain.cu:696-714: saxpy(-1) then sdot of the difference).
     float part = 0.f;
@@ -462,70 +575,144 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
     for (int off = 16; off >= 1; off >>= 1) part = __fadd_rn(part, __shfl_xor_sync(0xffffffffu, part, off));
     if ((tid & 31) == 0) s_part[tid >> 5] = part;
     __syncthreads();
-    if (tid != 0) return;
 
-    float norm_sq = 0.f;
+    if (tid == 0) {
+        float norm_sq = 0.f;
 #pragma unroll
-    for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);
+        for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);
 
-    const int y_hi = a.y[i_hi - a.res0], y_lo = a.y[i_lo - a.res0];
-    const float a_hi_old = a.alpha[i_hi - a.res0], a_lo_old = a.alpha[i_lo - a.res0];
-    float a_hi_new, a_lo_new, eta = 0.f;
-    if (a.directed) {
-        a_hi_new = a.dir_a_hi; a_lo_new = a.dir_a_lo;
-    } else {
-        // eta = K(hi,hi) + K(lo,lo) - 2 K(lo,hi)  (svmTrainMain.cpp:282); K(i,i) = exp(-gamma*0) = 1.
-        // K = (float)exp(-1 * (float)gamma * norm_sq): float product, double exp (svmTrain.cu:709).
-        const float k_lh = (float)exp((double)__fmul_rn(-a.gamma, norm_sq));
-        eta = __fsub_rn(__fadd_rn(1.0f, 1.0f), __fmul_rn(2.0f, k_lh));
-        // svmTrainMain.cpp:289-295; IEEE division (eta == 0 gives +-inf, clipped to 0 or C)
-        const float s = (float)(y_lo * y_hi);
-        const float a_lo_unc = __fadd_rn(a_lo_old, __fdiv_rn(__fmul_rn((float)y_lo, __fsub_rn(b_hi, b_lo)), eta));
-        const float a_hi_unc = __fadd_rn(a_hi_old, __fmul_rn(s, __fsub_rn(a_lo_old, a_lo_unc)));
-        a_lo_new = a_lo_unc < 0.0f ? 0.0f : (a_lo_unc > a.c ? a.c : a_lo_unc);
-        a_hi_new = a_hi_unc < 0.0f ? 0.0f : (a_hi_unc > a.c ? a.c : a_hi_unc);
-    }
-    // alpha[max_idx] = alpha_lo_new; alpha[min_idx] = alpha_hi_new   (svmTrainMain.cpp:298-299)
-    a.alpha[i_lo - a.res0] = a_lo_new;
-    a.alpha[i_hi - a.res0] = a_hi_new;
+        const int y_hi = (int)s_scal[0], y_lo = (int)s_scal[1];
+        const float a_hi_old = s_scal[2], a_lo_old = s_scal[3];
+        float a_hi_new, a_lo_new, eta = 0.f;
+        if (a.directed) {
+            a_hi_new = a.dir_a_hi; a_lo_new = a.dir_a_lo;
+        } else {
+            // eta = K(hi,hi) + K(lo,lo) - 2 K(lo,hi)  (svmTrainMain.cpp:282); K(i,i) = exp(-gamma*0) = 1.
+            // K = (float)exp(-1 * (float)gamma * norm_sq): float product, double exp (svmTrain.cu:709).
+            const float k_lh = (float)exp((double)__fmul_rn(-a.gamma, norm_sq));
+            eta = __fsub_rn(__fadd_rn(1.0f, 1.0f), __fmul_rn(2.0f, k_lh));
+            // svmTrainMain.cpp:289-295; IEEE division (eta == 0 gives +-inf, clipped to 0 or C)
+            const float s = (float)(y_lo * y_hi);
+            const float a_lo_unc = __fadd_rn(a_lo_old, __fdiv_rn(__fmul_rn((float)y_lo, __fsub_rn(b_hi, b_lo)), eta));
+            const float a_hi_unc = __fadd_rn(a_hi_old, __fmul_rn(s, __fsub_rn(a_lo_old, a_lo_unc)));
+            a_lo_new = a_lo_unc < 0.0f ? 0.0f : (a_lo_unc > a.c ? a.c : a_lo_unc);
+            a_hi_new = a_hi_unc < 0.0f ? 0.0f : (a_hi_unc > a.c ? a.c : a_hi_unc);
+        }
+        // alpha[max_idx] = alpha_lo_new; alpha[min_idx] = alpha_hi_new   (svmTrainMain.cpp:298-299)
+        // (multi-GPU: every rank computes the same values, the owner of the row stores them)
+        if (a.world <= 1 || (i_lo >= a.own0 && i_lo < a.own0 + a.own_n)) a.alpha[r_lo] = a_lo_new;
+        if (a.world <= 1 || (i_hi >= a.own0 && i_hi < a.own0 + a.own_n)) a.alpha[r_hi] = a_hi_new;
 
-    PassScalars ps;
-    ps.active = 1;
-    ps.delta_hi = __fmul_rn(__fsub_rn(a_hi_new, a_hi_old), (float)y_hi);
-    ps.delta_lo = __fmul_rn(__fsub_rn(a_lo_new, a_lo_old), (float)y_lo);
-    ps.xsq_hi = a.xsq[i_hi - a.res0];
-    ps.xsq_lo = a.xsq[i_lo - a.res0];
-    ps.line_hi = nullptr; ps.line_lo = nullptr; ps.both_hit = 0;
-    if (a.cache.lines > 0) {
-        // lookup order hi then lo (svmTrain.cu:203,238)
-        int hit_hi, hit_lo;
-        const int l_hi = cache_lookup_device(a.cache, i_hi, &hit_hi);
-        const int l_lo = cache_lookup_device(a.cache, i_lo, &hit_lo);
-        st->cache_lookups += 2;
-        st->cache_hits += hit_hi + hit_lo;
-        float* p_hi = a.cache.data + (size_t)l_hi * a.cache.line_stride;
-        float* p_lo = a.cache.data + (size_t)l_lo * a.cache.line_stride;
-        if (hit_hi && hit_lo) { ps.both_hit = 1; ps.line_hi = p_hi; ps.line_lo = p_lo; }
-        else { if (!hit_hi) ps.line_hi = p_hi; if (!hit_lo && l_lo != l_hi) ps.line_lo = p_lo; }
+        PassScalars ps;
+        ps.active = 1;
+        // when hi and lo are the same row the second store above wins; old values were read before both
+        ps.delta_hi = __fmul_rn(__fsub_rn(a_hi_new, a_hi_old), (float)y_hi);
+        ps.delta_lo = __fmul_rn(__fsub_rn(a_lo_new, a_lo_old), (float)y_lo);
+        ps.xsq_hi = s_scal[4];
+        ps.xsq_lo = s_scal[5];
+        ps.line_hi = nullptr; ps.line_lo = nullptr; ps.both_hit = 0;
+        if (cache_on) {
+            CacheDev cd = a.cache;
+            if (staged) {
+                const int L = a.cache.lines;
+                cd.key_of_line = s_cache; cd.prev = s_cache + L; cd.next = s_cache + 2 * L; cd.meta = s_cache + 3 * L;
+            }
+            // lookup order hi then lo (svmTrain.cu:203,238); the second lookup must see the first one's eviction
+            int hit_hi, hit_lo;
+            const int known_hi = __float_as_int(s_scal[6]);
+            const int l_hi = cache_lookup_device(cd, i_hi, known_hi, &hit_hi);
+            int known_lo = __float_as_int(s_scal[7]);
+            if (i_lo == i_hi) known_lo = l_hi;
+            else if (known_lo == l_hi) known_lo = -1;          // hi just took over lo's line
+            const int l_lo = cache_lookup_device(cd, i_lo, known_lo, &hit_lo);
+            st->cache_lookups += 2;
+            st->cache_hits += hit_hi + hit_lo;
+            float* p_hi = a.cache.data + (size_t)l_hi * a.cache.line_stride;
+            float* p_lo = a.cache.data + (size_t)l_lo * a.cache.line_stride;
+            if (hit_hi && hit_lo) { ps.both_hit = 1; ps.line_hi = p_hi; ps.line_lo = p_lo; }
+            else { if (!hit_hi) ps.line_hi = p_hi; if (!hit_lo && l_lo != l_hi) ps.line_lo = p_lo; }
+        }
+        st->pass = ps;
+        st->i_hi = i_hi; st->i_lo = i_lo; st->eta = eta;
+        const int it = num_iter + 1;
+        st->num_iter = it;
+        if (!a.directed) {
+            st->b_hi = b_hi; st->b_lo = b_lo;
+            // while (b_lo > b_hi + 2*epsilon && num_iter < max_iter)   (svmTrainMain.cpp:310)
+            const bool keep_going = b_lo > __fadd_rn(b_hi, __fmul_rn(2.0f, a.epsilon));
+            if (!keep_going) { st->converged = 1; st->done = 1; }
+            if (it >= a.max_iter) st->done = 1;
+        }
+        if (a.world <= 1) {               // (multi-GPU: the pack kernel consumed and reset the local keys)
+            a.keys[0] = DPSVM_KEY_EMPTY;
+            a.keys[1] = DPSVM_KEY_EMPTY;
+        }
     }
-    st->pass = ps;
-    st->i_hi = i_hi; st->i_lo = i_lo; st->eta = eta;
-    const int it = st->num_iter + 1;
-    st->num_iter = it;
-    if (!a.directed) {
-        st->b_hi = b_hi; st->b_lo = b_lo;
-        // while (b_lo > b_hi + 2*epsilon && num_iter < max_iter)   (svmTrainMain.cpp:310)
-        const bool keep_going = b_lo > __fadd_rn(b_hi, __fmul_rn(2.0f, a.epsilon));
-        if (!keep_going) { st->converged = 1; st->done = 1; }
-        if (it >= a.max_iter) st->done = 1;
+    if (staged) {
+        __syncthreads();
+        const int L = a.cache.lines;
+        for (int i = tid; i < L; i += kCtlThreads) {
+            a.cache.key_of_line[i] = s_cache[i];
+            a.cache.prev[i] = s_cache[L + i];
+            a.cache.next[i] = s_cache[2 * L + i];
+        }
+        if (tid < kCacheMetaInts) a.cache.meta[tid] = s_cache[3 * L + tid];
     }
-    a.keys[0] = DPSVM_KEY_EMPTY;
-    a.keys[1] = DPSVM_KEY_EMPTY;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Multi-GPU: publish this rank's candidates (keys, scalars, both rows) as one package and reset the
+// local keys.  One block.  An empty local set still ships a valid row (the first owned one) so the
+// reference's "index 0, +-1e9" default (svmTrainMain.cpp:249-252) stays well defined.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCtlThreads, 1) smo_pack_kernel(const PackDev a)
+{
+    const int tid = threadIdx.x;
+    const unsigned long long k_up = a.keys[0], k_low = a.keys[1];
+    float f_dummy;
+    int i_hi = a.own0, i_lo = a.own0;
+    if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_hi);
+    if (k_low != DPSVM_KEY_EMPTY) unpack_key_low(k_low, &f_dummy, &i_lo);
+    const int r_hi = i_hi - a.res0, r_lo = i_lo - a.res0;
+    CandHeader* h = reinterpret_cast<CandHeader*>(a.send);
+    float* rows = reinterpret_cast<float*>(h + 1);
+    const float* src_hi = a.x + (size_t)r_hi * a.pitch;
+    const float* src_lo = a.x + (size_t)r_lo * a.pitch;
+    for (int i = tid; i < a.pitch; i += kCtlThreads) {
+        rows[i] = src_hi[i];
+        rows[a.pitch + i] = src_lo[i];
+    }
+    if (tid == 0) {
+        h->key_up = k_up; h->key_low = k_low;
+        h->a_hi = a.alpha[r_hi]; h->a_lo = a.alpha[r_lo];
+        h->y_hi = a.y[r_hi]; h->y_lo = a.y[r_lo];
+        h->xsq_hi = a.xsq[r_hi]; h->xsq_lo = a.xsq[r_lo];
+    }
+    __syncthreads();
+    if (tid == 0) { a.keys[0] = DPSVM_KEY_EMPTY; a.keys[1] = DPSVM_KEY_EMPTY; }
 }
 
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
+// Launch with (optionally) the programmatic-stream-serialization attribute: the kernel may become
+// resident before its predecessor in the stream has finished; it orders itself with griddepcontrol.wait.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_ex(void (*kernel)(KArgs...), int blocks, int threads, size_t smem, cudaStream_t s, bool pdl, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 static int g_num_sms = 0;
 int device_sm_count()
 {
@@ -540,7 +727,7 @@ int device_sm_count()
 }
 
 template <int LPR, int ITERS>
-static cudaError_t launch_pass_t(const PassDev& a, cudaStream_t s)
+static cudaError_t launch_pass_t(PassDev a, int variant, cudaStream_t s)
 {
     constexpr int RPW = (32 / LPR) * kRowsInFlight;
     const int n_units = (a.n + RPW - 1) / RPW;
@@ -548,29 +735,38 @@ static cudaError_t launch_pass_t(const PassDev& a, cudaStream_t s)
     const int cap = device_sm_count() * 2;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    smo_pass_kernel<LPR, ITERS><<<blocks, kPassThreads, 0, s>>>(a);
-    return cudaGetLastError();
+    // variant: bit 0 = reverse sweep, bit 1 = L2 eviction hints with (variant >> 8) MB of X pinned
+    a.reverse = variant & 1;
+    const bool hint = (variant & 2) != 0;
+    if (hint) {
+        const double pin_bytes = (double)((variant >> 8) & 0xFFFFF) * 1e6;
+        const double unit_bytes = (double)RPW * a.pitch4 * 16.0;
+        double pu = pin_bytes / unit_bytes;
+        a.pin_units = pu > (double)n_units ? n_units : (int)pu;
+        return launch_ex(smo_pass_kernel<LPR, ITERS, true>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+    }
+    a.pin_units = 0;
+    return launch_ex(smo_pass_kernel<LPR, ITERS, false>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
 }
 
 template <int LPR>
-static cudaError_t launch_pass_lpr(int iters, const PassDev& a, cudaStream_t s)
+static cudaError_t launch_pass_lpr(int iters, const PassDev& a, int variant, cudaStream_t s)
 {
     switch (iters) {
-        case 1: return launch_pass_t<LPR, 1>(a, s);
-        case 2: return launch_pass_t<LPR, 2>(a, s);
-        case 3: return launch_pass_t<LPR, 3>(a, s);
-        case 4: return launch_pass_t<LPR, 4>(a, s);
-        case 5: return launch_pass_t<LPR, 5>(a, s);
-        case 6: return launch_pass_t<LPR, 6>(a, s);
-        case 7: return launch_pass_t<LPR, 7>(a, s);
-        case 8: return launch_pass_t<LPR, 8>(a, s);
+        case 1: return launch_pass_t<LPR, 1>(a, variant, s);
+        case 2: return launch_pass_t<LPR, 2>(a, variant, s);
+        case 3: return launch_pass_t<LPR, 3>(a, variant, s);
+        case 4: return launch_pass_t<LPR, 4>(a, variant, s);
+        case 5: return launch_pass_t<LPR, 5>(a, variant, s);
+        case 6: return launch_pass_t<LPR, 6>(a, variant, s);
+        case 7: return launch_pass_t<LPR, 7>(a, variant, s);
+        case 8: return launch_pass_t<LPR, 8>(a, variant, s);
     }
     return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s)
 {
-    (void)variant;
     if (a.n <= 0) return cudaSuccess;
     if (a.pitch4 > 256) {
         const int cap4 = ((a.pitch4 + 31) / 32) * 32;
@@ -586,15 +782,14 @@ cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s)
         int blocks = (n_units + 7) / 8;
         const int cap = device_sm_count() * 2;
         if (blocks > cap) blocks = cap;
-        smo_pass_generic_kernel<<<blocks, kPassThreads, smem, s>>>(a);
-        return cudaGetLastError();
+        return launch_ex(smo_pass_generic_kernel, blocks, kPassThreads, smem, s, a.pdl != 0, a);
     }
     const DotGeom g = dot_geometry(a.pitch4);
     switch (g.lpr) {
-        case 4: return launch_pass_lpr<4>(g.iters, a, s);
-        case 8: return launch_pass_lpr<8>(g.iters, a, s);
-        case 16: return launch_pass_lpr<16>(g.iters, a, s);
-        default: return launch_pass_lpr<32>(g.iters, a, s);
+        case 4: return launch_pass_lpr<4>(g.iters, a, variant, s);
+        case 8: return launch_pass_lpr<8>(g.iters, a, variant, s);
+        case 16: return launch_pass_lpr<16>(g.iters, a, variant, s);
+        default: return launch_pass_lpr<32>(g.iters, a, variant, s);
     }
 }
 
@@ -671,10 +866,17 @@ cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStre
     return cudaGetLastError();
 }
 
+cudaError_t launch_pack(const PackDev& a, cudaStream_t s)
+{
+    smo_pack_kernel<<<1, kCtlThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_control(const CtlDev& a, cudaStream_t s)
 {
-    smo_control_kernel<<<1, kCtlThreads, 0, s>>>(a);
-    return cudaGetLastError();
+    const bool staged = a.cache.lines > 0 && a.cache.lines <= kCacheSmemLines;
+    const size_t smem = staged ? sizeof(int) * (3 * (size_t)a.cache.lines + kCacheMetaInts) : 0;
+    return launch_ex(smo_control_kernel, 1, kCtlThreads, smem, s, a.pdl != 0, a);
 }
 
 }  // namespace dpsvm

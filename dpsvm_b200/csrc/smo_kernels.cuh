@@ -8,6 +8,7 @@ namespace dpsvm {
 constexpr int kPassThreads = 256;
 constexpr int kRowsInFlight = 2;   // rows per lane group whose loads are issued before any FMA
 constexpr int kCtlThreads = 256;
+constexpr int kCacheSmemLines = 3584;   // caches up to this many lines keep their recency lists in smem during the control step
 
 // Arguments of the fused pass kernel (by value; small enough for the parameter space).
 struct PassDev {
@@ -22,6 +23,10 @@ struct PassDev {
     float gamma, c;
     int index_base;
     unsigned long long* keys;   // [2]
+    int reverse;                // sweep units back to front (set by the launcher from `variant`)
+    int pin_units;              // units below this index are loaded L2::evict_last (HINT kernels)
+    int early_load;             // issue the first unit's X loads before reading the pass scalars
+    int pdl;                    // launch with programmatic dependent launch (host-side flag)
     PassScalars imm;            // used when dev == nullptr
     const PassScalars* dev;     // device-resident scalars written by the control kernel
 };
@@ -40,6 +45,30 @@ struct CacheDev {
     int* meta;              // [kCacheMetaInts]: size, head (LRU), tail (MRU)
 };
 
+// Candidate package one rank publishes per iteration in the multi-GPU loop: its local selection
+// (packed keys), the scalars of the two candidate rows and the rows themselves.  Replaces the
+// 4-float rv[] of the reference's Allgather (svmTrainMain.cpp:244) -- the rows ride along so that no
+// second, data-dependent broadcast is needed.
+struct CandHeader {
+    unsigned long long key_up, key_low;
+    float a_hi, a_lo;        // alpha of the local candidates
+    int y_hi, y_lo;
+    float xsq_hi, xsq_lo;
+    int pad[6];
+};
+static_assert(sizeof(CandHeader) == 64, "CandHeader is 64 bytes");
+inline size_t cand_package_bytes(int pitch) { return sizeof(CandHeader) + 2 * sizeof(float) * (size_t)pitch; }
+
+struct PackDev {
+    unsigned long long* keys;   // [2] local selection; reset to empty by the pack kernel
+    const float* x;             // resident rows (global row res0 first)
+    int pitch, res0, own0;      // own0 = first owned global row (fallback candidate when a set is empty)
+    const float* xsq;
+    const int* y;
+    const float* alpha;
+    unsigned char* send;        // one package
+};
+
 struct CtlDev {
     DevState* st;
     unsigned long long* keys;   // [2] local selection result of the previous pass
@@ -56,6 +85,12 @@ struct CtlDev {
     int directed;               // host-directed update (SvmTrain::train_step2)
     int dir_i_hi, dir_i_lo;
     float dir_a_hi, dir_a_lo;
+    int pdl;                    // launch with programmatic dependent launch (host-side flag)
+    // multi-GPU: world > 1 -> the selection comes from `world` gathered candidate packages
+    int world;
+    const unsigned char* cand;  // [world x cand_stride]
+    size_t cand_stride;
+    int own0, own_n;            // owned global row range: only the owner installs a new alpha
     const float* ext_row_hi;    // optional externally supplied rows (device pointers)
     const float* ext_row_lo;
 };
@@ -67,6 +102,7 @@ cudaError_t launch_init_state(const int* y, int n, float* alpha, float* f, cudaS
 cudaError_t launch_select(const float* alpha, const int* y, const float* f, int n, float c, int index_base,
                           unsigned long long* keys, cudaStream_t s);
 cudaError_t launch_control(const CtlDev& a, cudaStream_t s);
+cudaError_t launch_pack(const PackDev& a, cudaStream_t s);
 cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStream_t s);
 
 }  // namespace dpsvm

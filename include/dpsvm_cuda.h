@@ -67,6 +67,11 @@ int dpsvm_alpha_update(float eta, int y_hi, int y_lo, float b_hi, float b_lo, fl
 /* Row pitch (floats) used for a given attribute count: d rounded up to a multiple of 4. */
 int dpsvm_pitch_for(int d);
 
+/* The `variant` word the trainer uses for the fused pass of iteration number `iteration_parity` on a
+ * shard of n rows: bit 0 = sweep back to front (serpentine order across iterations), bit 1 = L2
+ * eviction-priority hints with (variant >> 8) MB of X kept resident.  Results do not depend on it. */
+int dpsvm_pass_variant(int n, int pitch, int iteration_parity);
+
 /* Packed selection keys: (orderable(f) << 32) | index for I_up, (orderable(-f) << 32) | index for
  * I_low, so that an unsigned 64-bit MIN yields argmin f / argmax f with the lowest index among
  * equal values (north_star's tie rule; replaces i_helper, svmTrain.h:24-37, and my_maxmin,
@@ -124,7 +129,7 @@ typedef struct {
     uint64_t* d_keys;        /* [2] in/out */
     float* d_line_hi;        /* optional [n] */
     float* d_line_lo;        /* optional [n] */
-    int variant;             /* 0 = default; see DESIGN.md (kernel variants for A/B timing) */
+    int variant;             /* 0 = plain forward sweep; see dpsvm_pass_variant */
 } dpsvm_pass_args;
 
 int dpsvm_smo_pass(const dpsvm_pass_args* args, void* stream);
