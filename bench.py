@@ -337,7 +337,7 @@ def main():
             traffic = json.load(fh).get(args.workload if world == 1 else "%s_p%d" % (args.workload, world))
     except Exception:
         pass
-    kernels_per_iter = 2 if world == 1 else 3
+    kernels_per_iter = 3 if tr.comm_transport == "nccl" else 2     # control + pass (+ pack before the NCCL all-gather)
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -346,7 +346,7 @@ def main():
             "workload": "%s %dx%d RBF c=%g gamma=%g eps=%g" % (args.workload, n_total, d, prm["c"], prm["gamma"], prm["epsilon"]),
             "iters_per_step": ips, "iterations_timed": done_iters, "converged_during_timing": bool(st.converged),
             "cache_lines": args.cache_size, "cache_hits": int(st.cache_hits), "cache_lookups": int(st.cache_lookups),
-            "rows_per_gpu": n_shard, "us_per_iteration": 1e3 * iter_ms,
+            "rows_per_gpu": n_shard, "us_per_iteration": 1e3 * iter_ms, "exchange": tr.comm_transport,
             "l2": "X shard %.1f MB per pass vs 126 MB L2: %s" % (4e-6 * n_shard * d, "inputs larger than L2" if 4.0 * n_shard * d > 126e6 else "L2-resident"),
             "iteration_GBps_incl_control": abytes / (iter_ms * 1e-3) / 1e9,
         },

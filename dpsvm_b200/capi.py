@@ -69,7 +69,7 @@ EXPORTS = [
     "dpsvm_row_norms", "dpsvm_init_state", "dpsvm_select", "dpsvm_smo_pass", "dpsvm_create", "dpsvm_destroy",
     "dpsvm_upload", "dpsvm_upload_device", "dpsvm_reset", "dpsvm_step1", "dpsvm_step2", "dpsvm_train",
     "dpsvm_train_async", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
-    "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init", "dpsvm_smo_iteration_noalloc",
+    "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init", "dpsvm_comm_transport", "dpsvm_smo_iteration_noalloc",
 ]
 
 _lib = None
@@ -115,6 +115,7 @@ def lib():
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_float)]
         L.dpsvm_comm_unique_id.argtypes = [C.c_void_p]
         L.dpsvm_comm_init.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.dpsvm_comm_transport.argtypes = [C.c_void_p]
         L.dpsvm_shard_layout.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.dpsvm_merge_candidates.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                              C.POINTER(C.c_float), C.POINTER(C.c_float)]
@@ -335,6 +336,10 @@ class Trainer:
     def comm_init(self, id_bytes: bytes, rank: int, world: int):
         buf = (C.c_ubyte * COMM_ID_BYTES).from_buffer_copy(id_bytes)
         check(lib().dpsvm_comm_init(self._h, buf, rank, world))
+
+    @property
+    def comm_transport(self) -> str:
+        return {0: "none", 1: "nccl", 2: "p2p"}[lib().dpsvm_comm_transport(self._h)]
 
 
 def comm_unique_id() -> bytes:

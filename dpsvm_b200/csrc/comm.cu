@@ -2,19 +2,27 @@
 //
 // Replaces the per-iteration OpenMPI Allgather of the reference (svmTrainMain.cpp:244: 4 floats per
 // rank over TCP, indices carried as floats) and the host merge that follows it (:255-274).
-// Per iteration, captured in the same CUDA graph as the kernels:
-//     pack kernel     -> this rank's package: packed keys + scalars + the two candidate rows
-//     ncclAllGather   -> every rank holds all P packages (NVLink / NVSwitch)
-//     control kernel  -> identical merge + eta + alpha update on every rank (as the reference does
-//                        redundantly on every host, svmTrainMain.cpp:279-299); owners store alpha
-//     fused pass      -> over the rank's own shard
-// The rows ride in the package, so no second, data-dependent broadcast of the selected feature
-// vectors is needed (its root would only be known on the device).
+// Every rank publishes, once per iteration, a "candidate package": its packed local selection keys,
+// the scalars of its two candidate rows and the rows themselves -- so no second, data-dependent
+// broadcast of the selected feature vectors is needed (its root would only be known on the device).
+// Every rank then runs the identical merge + eta + alpha update (as the reference does redundantly
+// on every host, svmTrainMain.cpp:279-299); the owner of a row stores its new alpha.
 //
-// NCCL is bound at run time with dlopen("libnccl.so.2"): the library has no link-time dependency on
-// it, single-GPU users never load it, and inside a PyTorch process the already-loaded NCCL is reused.
+// Two transports:
+//   p2p  (default)  fused with the pass: the last CTA of the pass to finish stores the package
+//                   straight into every rank's mailbox (CUDA-IPC-mapped peer memory, NVLink /
+//                   NVSwitch) and raises a flag; the next control kernel waits on the flags.
+//                   Per iteration: control, pass -- two kernels, no collective call.
+//   nccl            pack kernel -> ncclAllGather -> control -> pass, all captured in the graph.
+//                   (DPSVM_EXCHANGE=nccl, or automatically when peer mapping is unavailable.)
+// NCCL is always used for the bootstrap (IPC handle exchange, barriers).  It is bound at run time
+// with dlopen("libnccl.so.2"): no link-time dependency, single-GPU users never load it, and inside a
+// PyTorch process the already-loaded NCCL is reused.
 #include <dlfcn.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <vector>
 
 #include "dpsvm_internal.cuh"
 
@@ -61,12 +69,98 @@ int load_nccl()
     return DPSVM_OK;
 }
 
+constexpr size_t kFlagBytes = 1024;      // flags [2][world] u32 at the head of the mailbox allocation
+
 struct CommState {
     ncclComm_t comm = nullptr;
+    size_t package = 0;
+    // nccl transport
     unsigned char* d_send = nullptr;     // one package
     unsigned char* d_recv = nullptr;     // world packages
-    size_t package = 0;
+    // p2p transport
+    bool p2p = false;
+    unsigned char* d_box = nullptr;      // [kFlagBytes flags][2][world][package]
+    unsigned int* d_counter = nullptr;
+    PushDev* d_push = nullptr;
+    void* opened[kMaxPeers] = {};
+    unsigned char* d_tmp = nullptr;      // bootstrap all-gather buffer
 };
+
+int nccl_gather_bytes(dpsvm_ctx* c, CommState* s, const void* h_in, void* h_out, size_t bytes)
+{
+    // bootstrap helper: all-gather `bytes` host bytes per rank through device memory; synchronous
+    const size_t total = bytes * (size_t)c->world;
+    unsigned char* d = nullptr;
+    if (cudaMalloc(&d, total + bytes) != cudaSuccess) return fail(DPSVM_ERR_NOMEM, "comm bootstrap: cudaMalloc");
+    cudaError_t e = cudaMemcpyAsync(d + total, h_in, bytes, cudaMemcpyHostToDevice, c->stream);
+    ncclResult_t r = 0;
+    if (e == cudaSuccess) r = g_nccl.AllGather(d + total, d, bytes, ncclChar, s->comm, c->stream);
+    if (e == cudaSuccess && r == 0) e = cudaMemcpyAsync(h_out, d, total, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && r == 0) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (r != 0) return fail(DPSVM_ERR_COMM, "comm bootstrap all-gather: %s", g_nccl.GetErrorString(r));
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "comm bootstrap: %s", cudaGetErrorString(e));
+    return DPSVM_OK;
+}
+
+// Map every peer's mailbox.  Returns 1 when this rank succeeded, 0 otherwise (never an error: the
+// caller falls back to the NCCL transport when any rank reports 0).
+int try_setup_p2p(dpsvm_ctx* c, CommState* s)
+{
+    const int world = c->world;
+    if (world > kMaxPeers) return 0;
+    const size_t box_bytes = kFlagBytes + 2 * (size_t)world * s->package;
+    // every rank performs the same collective calls whatever happens locally (a local failure only
+    // turns this rank's vote into 0)
+    int ok = 1;
+    if (cudaMalloc(&s->d_box, box_bytes) != cudaSuccess || cudaMalloc(&s->d_counter, sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc(&s->d_push, sizeof(PushDev)) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+    }
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    if (ok) {
+        cudaMemset(s->d_box, 0, box_bytes);
+        cudaMemset(s->d_counter, 0, sizeof(unsigned int));
+        if (cudaIpcGetMemHandle(&mine, s->d_box) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+    }
+    std::vector<cudaIpcMemHandle_t> all((size_t)world);
+    if (nccl_gather_bytes(c, s, &mine, all.data(), sizeof(mine)) != DPSVM_OK) return 0;
+    PushDev h{};
+    h.counter = s->d_counter;
+    h.keys = c->d_keys;
+    h.x = c->d_x;
+    h.pitch = c->pitch;
+    h.res0 = c->res0;
+    h.own0 = c->p.shard_start;
+    h.xsq = c->d_xsq;
+    h.y = c->d_y;
+    h.alpha = c->d_alpha;
+    h.st = c->d_st;
+    h.world = world;
+    h.rank = c->rank;
+    h.package = s->package;
+    for (int q = 0; q < world && ok; ++q) {
+        unsigned char* base = nullptr;
+        if (q == c->rank) {
+            base = s->d_box;
+        } else {
+            void* p = nullptr;
+            if (cudaIpcOpenMemHandle(&p, all[(size_t)q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                ok = 0;
+                break;
+            }
+            s->opened[q] = p;
+            base = static_cast<unsigned char*>(p);
+        }
+        h.peer_flag[q] = reinterpret_cast<unsigned int*>(base);
+        h.peer_mail[q] = base + kFlagBytes;
+    }
+    if (ok && cudaMemcpy(s->d_push, &h, sizeof(h), cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+    return ok;
+}
 
 }  // namespace
 
@@ -74,39 +168,66 @@ void comm_free(dpsvm_ctx* c)
 {
     CommState* s = static_cast<CommState*>(c->comm);
     if (!s) return;
+    for (int q = 0; q < kMaxPeers; ++q) if (s->opened[q]) cudaIpcCloseMemHandle(s->opened[q]);
     if (s->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(s->comm);
-    cudaFree(s->d_send);
-    cudaFree(s->d_recv);
+    cudaFree(s->d_send); cudaFree(s->d_recv); cudaFree(s->d_box); cudaFree(s->d_counter); cudaFree(s->d_push);
     delete s;
     c->comm = nullptr;
+    c->d_push = nullptr;
 }
 
-// One iteration of the sharded loop: pack -> all-gather -> control -> pass.
+// After the local (re)selection at setup/reset: make the first package available to every rank.
+int comm_after_select(dpsvm_ctx* c)
+{
+    CommState* s = static_cast<CommState*>(c->comm);
+    if (!s || !s->p2p) return DPSVM_OK;
+    // clear my flags, then a barrier (an all-gather completes only after every rank has contributed,
+    // i.e. after every rank's clear is ordered before its contribution), then the initial push
+    cudaError_t e = cudaMemsetAsync(s->d_box, 0, kFlagBytes, c->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned int), c->stream);
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "comm reset: %s", cudaGetErrorString(e));
+    ncclResult_t r = g_nccl.AllGather(s->d_send, s->d_recv, 8, ncclChar, s->comm, c->stream);
+    if (r != 0) return fail(DPSVM_ERR_COMM, "comm barrier: %s", g_nccl.GetErrorString(r));
+    e = launch_push(s->d_push, c->stream);
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "initial push: %s", cudaGetErrorString(e));
+    e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "initial push: %s", cudaGetErrorString(e));
+    return DPSVM_OK;
+}
+
+// One iteration of the sharded loop.
 int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t stream, int variant)
 {
     CommState* s = static_cast<CommState*>(c->comm);
     if (!s || !s->comm) return fail(DPSVM_ERR_COMM, "multi-GPU exchange not initialised (dpsvm_comm_init)");
-    PackDev p{};
-    p.keys = c->d_keys;
-    p.x = c->d_x;
-    p.pitch = c->pitch;
-    p.res0 = c->res0;
-    p.own0 = c->p.shard_start;
-    p.xsq = c->d_xsq;
-    p.y = c->d_y;
-    p.alpha = c->d_alpha;
-    p.send = s->d_send;
-    cudaError_t e = launch_pack(p, stream);
-    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "pack launch: %s", cudaGetErrorString(e));
-    ncclResult_t r = g_nccl.AllGather(s->d_send, s->d_recv, s->package, ncclChar, s->comm, stream);
-    if (r != 0) return fail(DPSVM_ERR_COMM, "ncclAllGather: %s", g_nccl.GetErrorString(r));
     CtlDev ctl = make_ctl_args(c);
     ctl.world = c->world;
-    ctl.cand = s->d_recv;
     ctl.cand_stride = s->package;
     ctl.own0 = c->p.shard_start;
     ctl.own_n = c->p.shard_rows;
-    ctl.pdl = 0;                       // its predecessor is an NCCL kernel: plain stream order
+    cudaError_t e;
+    if (s->p2p) {
+        ctl.cand = s->d_box + kFlagBytes;
+        ctl.flags = reinterpret_cast<const unsigned int*>(s->d_box);
+    } else {
+        PackDev p{};
+        p.keys = c->d_keys;
+        p.x = c->d_x;
+        p.pitch = c->pitch;
+        p.res0 = c->res0;
+        p.own0 = c->p.shard_start;
+        p.xsq = c->d_xsq;
+        p.y = c->d_y;
+        p.alpha = c->d_alpha;
+        p.send = s->d_send;
+        e = launch_pack(p, stream);
+        if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "pack launch: %s", cudaGetErrorString(e));
+        ncclResult_t r = g_nccl.AllGather(s->d_send, s->d_recv, s->package, ncclChar, s->comm, stream);
+        if (r != 0) return fail(DPSVM_ERR_COMM, "ncclAllGather: %s", g_nccl.GetErrorString(r));
+        ctl.cand = s->d_recv;
+        ctl.flags = nullptr;
+        ctl.pdl = 0;                   // its predecessor is an NCCL kernel: plain stream order
+    }
     e = launch_control(ctl, stream);
     if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "control launch: %s", cudaGetErrorString(e));
     e = launch_pass(make_pass_args(c), variant, stream);
@@ -161,5 +282,24 @@ extern "C" int dpsvm_comm_init(dpsvm_ctx* c, const unsigned char id[DPSVM_COMM_I
     c->comm = s;
     c->world = world;
     c->rank = rank;
+
+    // transport: peer memory unless told otherwise; every rank must agree, so the outcome is voted on
+    const char* ex = getenv("DPSVM_EXCHANGE");
+    int mine = (ex && strcmp(ex, "nccl") == 0) ? 0 : try_setup_p2p(c, s);
+    std::vector<int> votes((size_t)world, 0);
+    rc = nccl_gather_bytes(c, s, &mine, votes.data(), sizeof(int));
+    if (rc != DPSVM_OK) return rc;
+    bool all_ok = true;
+    for (int v : votes) all_ok = all_ok && v != 0;
+    s->p2p = all_ok;
+    c->d_push = all_ok ? s->d_push : nullptr;
+    c->exchange_p2p = all_ok ? 1 : 0;
+    if (c->uploaded) return comm_after_select(c);
     return DPSVM_OK;
+}
+
+extern "C" int dpsvm_comm_transport(dpsvm_ctx* c)
+{
+    if (!c || c->world <= 1 || !c->comm) return 0;
+    return c->exchange_p2p ? 2 : 1;
 }

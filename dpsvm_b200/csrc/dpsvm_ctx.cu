@@ -78,6 +78,7 @@ PassDev make_pass_args(dpsvm_ctx* c)
     // with a large cache a both-rows-cached iteration (no X sweep) is likely: do not pre-issue X loads
     a.early_load = c->cache.lines < 64;
     a.pdl = c->pdl;
+    a.push = c->d_push;
     return a;
 }
 
@@ -218,6 +219,7 @@ static int reset_state(dpsvm_ctx* c)
                      c->d_keys, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->target_iter = 0;
+    if (c->world > 1) return comm_after_select(c);
     return DPSVM_OK;
 }
 
@@ -478,6 +480,7 @@ int dpsvm_sync(dpsvm_ctx* c, dpsvm_train_status* status)
     CU(cudaStreamSynchronize(c->stream));
     c->target_iter = c->h_st[0].num_iter;
     fill_status(c->h_st[0], 0.f, status);
+    if (c->h_st[0].error) return fail(DPSVM_ERR_COMM, "multi-GPU exchange timed out waiting for a peer's candidates (iteration %d)", c->h_st[0].num_iter);
     return DPSVM_OK;
 }
 
@@ -523,6 +526,7 @@ int dpsvm_train(dpsvm_ctx* c, int max_new_iter, dpsvm_train_status* status)
     CU(cudaStreamSynchronize(c->stream));
     c->target_iter = c->h_st[0].num_iter;
     fill_status(c->h_st[0], ms, status);
+    if (c->h_st[0].error) return fail(DPSVM_ERR_COMM, "multi-GPU exchange timed out waiting for a peer's candidates (iteration %d)", c->h_st[0].num_iter);
     return DPSVM_OK;
 }
 

@@ -41,6 +41,8 @@ struct dpsvm_ctx {
     // multi-GPU
     int rank = 0, world = 1;
     void* comm = nullptr;        // opaque (comm.cu)
+    const dpsvm::PushDev* d_push = nullptr;   // peer-memory exchange descriptor (device), null otherwise
+    int exchange_p2p = 0;
 
     // predict scratch (predict.cu)
     void* predict = nullptr;
@@ -59,5 +61,6 @@ void predict_free(dpsvm_ctx* c);
 // comm.cu
 void comm_free(dpsvm_ctx* c);
 int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s, int variant);
+int comm_after_select(dpsvm_ctx* c);
 
 }  // namespace dpsvm

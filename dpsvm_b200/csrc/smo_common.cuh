@@ -109,7 +109,7 @@ struct DevState {
     float b_hi, b_lo;
     int i_hi, i_lo;
     float eta;
-    int pad0;
+    int error;             // 1: the peer exchange timed out (multi-GPU); the loop is stopped
     long long cache_hits;
     long long cache_lookups;
     PassScalars pass;

@@ -103,6 +103,85 @@ __device__ __forceinline__ void publish_keys(unsigned long long best_up, unsigne
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Peer-memory candidate exchange (multi-GPU).  Runs in ONE block: builds this rank's package from
+// the final local keys and stores it into slot (seq & 1) of every rank's mailbox -- stores to
+// CUDA-IPC-mapped peer memory travel over NVLink -- then raises this rank's flag there.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p)
+{
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ void pack_and_push(const PushDev& p)
+{
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    // final keys of this pass: every CTA fenced after its atomicMin and before taking its ticket
+    const unsigned long long k_up = __ldcg(p.keys), k_low = __ldcg(p.keys + 1);
+    const unsigned int seq = (unsigned int)__ldcg(&p.st->num_iter);
+    const unsigned int slot = seq & 1u;
+    float f_dummy;
+    int i_hi = p.own0, i_lo = p.own0;      // an empty set still ships a valid row (see smo_pack_kernel)
+    if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_hi);
+    if (k_low != DPSVM_KEY_EMPTY) unpack_key_low(k_low, &f_dummy, &i_lo);
+    const int r_hi = i_hi - p.res0, r_lo = i_lo - p.res0;
+    CandHeader h;
+    h.key_up = k_up; h.key_low = k_low;
+    h.a_hi = __ldcg(p.alpha + r_hi); h.a_lo = __ldcg(p.alpha + r_lo);
+    h.y_hi = __ldg(p.y + r_hi); h.y_lo = __ldg(p.y + r_lo);
+    h.xsq_hi = __ldg(p.xsq + r_hi); h.xsq_lo = __ldg(p.xsq + r_lo);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) h.pad[i] = 0;
+    const float4* src_hi = reinterpret_cast<const float4*>(p.x + (size_t)r_hi * p.pitch);
+    const float4* src_lo = reinterpret_cast<const float4*>(p.x + (size_t)r_lo * p.pitch);
+    const int pitch4 = p.pitch / 4;
+    const size_t slot_off = ((size_t)slot * p.world + p.rank) * p.package;
+    // each thread keeps its share of the two rows in registers and stores it to every peer
+    for (int i = tid; i < 2 * pitch4; i += nthr) {
+        const float4 v = (i < pitch4) ? __ldg(src_hi + i) : __ldg(src_lo + (i - pitch4));
+        for (int q = 0; q < p.world; ++q) {
+            float4* dst = reinterpret_cast<float4*>(p.peer_mail[q] + slot_off + sizeof(CandHeader));
+            dst[i] = v;
+        }
+    }
+    if (tid < p.world) {
+        const uint4* hs = reinterpret_cast<const uint4*>(&h);
+        uint4* dst = reinterpret_cast<uint4*>(p.peer_mail[tid] + slot_off);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dst[i] = hs[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < p.world) st_release_sys_u32(p.peer_flag[tid] + slot * p.world + p.rank, seq + 1u);
+    if (tid == 0) { p.keys[0] = DPSVM_KEY_EMPTY; p.keys[1] = DPSVM_KEY_EMPTY; }
+}
+
+// After publish_keys: the last CTA of the pass to get here publishes the candidates.
+__device__ __forceinline__ void push_if_last(const PushDev* push, int* s_flag)
+{
+    if (!push) return;
+    if (threadIdx.x == 0) {
+        __threadfence();                                   // my atomicMin before my ticket
+        const unsigned int t = atomicAdd(push->counter, 1u);
+        const int last = (t == gridDim.x - 1);
+        if (last) { *push->counter = 0; __threadfence(); } // see everyone's atomicMin; re-arm for the next pass
+        *s_flag = last;
+    }
+    __syncthreads();
+    if (*s_flag) pack_and_push(*push);
+}
+
+__global__ void __launch_bounds__(kCtlThreads, 1) smo_push_kernel(const PushDev* push)
+{
+    pack_and_push(*push);
+}
+
 // The per-row tail shared by every pass variant: kernel values, f update (update_functor,
 // svmTrain.cu:128-135), optional cache-line store, classification (arbitrary_functor, :53-91) and
 // the running packed-key minima.
@@ -177,6 +256,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev
     __shared__ __align__(16) float4 s_lo[CAP4];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
+    __shared__ int s_pushflag;
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane % LPR, grp = lane / LPR;
@@ -244,6 +324,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev
     if (sc.both_hit) {
         pass_both_hit(sc, a, best_up, best_low);
         publish_keys(best_up, best_low, a.keys, s_red);
+        push_if_last(a.push, &s_pushflag);
         return;
     }
 
@@ -285,6 +366,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev
         }
     }
     publish_keys(best_up, best_low, a.keys, s_red);
+    push_if_last(a.push, &s_pushflag);
 }
 
 // Same algorithm for rows too long for the unrolled variants (pitch4 > 256): runtime chunk loop.
@@ -294,6 +376,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
+    __shared__ int s_pushflag;
     const int cap4 = ((a.pitch4 + 31) / 32) * 32;
     float4* s_hi = reinterpret_cast<float4*>(dyn_smem);
     float4* s_lo = s_hi + cap4;
@@ -306,6 +389,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
     if (sc.both_hit) {
         pass_both_hit(sc, a, best_up, best_low);
         publish_keys(best_up, best_low, a.keys, s_red);
+        push_if_last(a.push, &s_pushflag);
         return;
     }
     stage_selected_rows(s_hi, s_lo, a.x_hi4, a.x_lo4, a.pitch4, cap4, &s_bar);
@@ -350,6 +434,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
         }
     }
     publish_keys(best_up, best_low, a.keys, s_red);
+    push_if_last(a.push, &s_pushflag);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -509,20 +594,46 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
     if (a.directed) {
         i_hi = a.dir_i_hi; i_lo = a.dir_i_lo; b_hi = 0.f; b_lo = 0.f;
     } else if (a.world > 1) {
+        const unsigned char* cand = a.cand + (a.flags ? (size_t)(num_iter & 1) * a.world * a.cand_stride : 0);
+        if (a.flags) {
+            // peer-memory exchange: wait until every rank's package for this iteration has landed in
+            // slot (num_iter & 1) of the local mailbox.  Bounded spin: a missing peer stops the loop
+            // (DevState::error) instead of hanging the GPU.
+            __shared__ int s_timeout;
+            if (tid == 0) s_timeout = 0;
+            __syncthreads();
+            if (tid < a.world) {
+                const unsigned int want = (unsigned int)num_iter + 1u;
+                const unsigned int* fl = a.flags + (size_t)(num_iter & 1) * a.world + tid;
+                unsigned long long t0 = 0;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                while (ld_acquire_sys_u32(fl) != want) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > 4000000000ull) { s_timeout = 1; break; }     // 4 s
+                    __nanosleep(64);
+                }
+            }
+            __syncthreads();
+            if (s_timeout) {
+                if (tid == 0) { st->error = 1; st->done = 1; st->pass.active = 0; }
+                return;
+            }
+        }
         // Global merge of the gathered packages (svmTrainMain.cpp:255-274): the minimum packed key is
         // argmin f / argmax f with the lowest GLOBAL index among equal values, identical on every rank.
         unsigned long long g_up = DPSVM_KEY_EMPTY, g_low = DPSVM_KEY_EMPTY;
         int w_up = 0, w_low = 0;
         for (int r = 0; r < a.world; ++r) {
-            const CandHeader* h = reinterpret_cast<const CandHeader*>(a.cand + (size_t)r * a.cand_stride);
-            const unsigned long long u = h->key_up, l = h->key_low;
+            const CandHeader* h = reinterpret_cast<const CandHeader*>(cand + (size_t)r * a.cand_stride);
+            const unsigned long long u = __ldcg(&h->key_up), l = __ldcg(&h->key_low);
             if (u < g_up) { g_up = u; w_up = r; }
             if (l < g_low) { g_low = l; w_low = r; }
         }
         unpack_key_up(g_up, &b_hi, &i_hi);
         unpack_key_low(g_low, &b_lo, &i_lo);
-        h_hi = reinterpret_cast<const CandHeader*>(a.cand + (size_t)w_up * a.cand_stride);
-        h_lo = reinterpret_cast<const CandHeader*>(a.cand + (size_t)w_low * a.cand_stride);
+        h_hi = reinterpret_cast<const CandHeader*>(cand + (size_t)w_up * a.cand_stride);
+        h_lo = reinterpret_cast<const CandHeader*>(cand + (size_t)w_low * a.cand_stride);
     } else {
         unpack_key_up(k_up, &b_hi, &i_hi);
         unpack_key_low(k_low, &b_lo, &i_lo);
@@ -869,6 +980,12 @@ cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStre
 cudaError_t launch_pack(const PackDev& a, cudaStream_t s)
 {
     smo_pack_kernel<<<1, kCtlThreads, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_push(const PushDev* d_push, cudaStream_t s)
+{
+    smo_push_kernel<<<1, kCtlThreads, 0, s>>>(d_push);
     return cudaGetLastError();
 }
 

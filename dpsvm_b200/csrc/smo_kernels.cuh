@@ -10,6 +10,8 @@ constexpr int kRowsInFlight = 2;   // rows per lane group whose loads are issued
 constexpr int kCtlThreads = 256;
 constexpr int kCacheSmemLines = 3584;   // caches up to this many lines keep their recency lists in smem during the control step
 
+struct PushDev;
+
 // Arguments of the fused pass kernel (by value; small enough for the parameter space).
 struct PassDev {
     const float4* x4;       // [n x pitch4] owned rows
@@ -29,6 +31,7 @@ struct PassDev {
     int pdl;                    // launch with programmatic dependent launch (host-side flag)
     PassScalars imm;            // used when dev == nullptr
     const PassScalars* dev;     // device-resident scalars written by the control kernel
+    const PushDev* push;        // multi-GPU peer-memory exchange: last CTA publishes the candidates (else null)
 };
 
 // Kernel-row cache (device-resident LRU).  line_of_key is a direct index over the GLOBAL row
@@ -69,6 +72,28 @@ struct PackDev {
     unsigned char* send;        // one package
 };
 
+// Peer-memory exchange (multi-GPU, one process per GPU): every rank owns a mailbox
+//   mail[2 slots][world][package]  and  flag[2 slots][world]
+// mapped into every peer with CUDA IPC.  The last CTA of a pass to finish writes this rank's package
+// straight into slot (seq & 1) of EVERY rank's mailbox over NVLink (plain stores to mapped peer
+// memory), fences, and raises its flag there to seq + 1; the next control kernel waits for all
+// `world` flags of that slot.  seq = DevState::num_iter, which every rank advances identically.
+constexpr int kMaxPeers = 16;
+struct PushDev {
+    unsigned int* counter;          // CTAs of the current pass that have finished
+    unsigned long long* keys;       // [2] local selection; reset to empty after packing
+    const float* x;                 // resident rows (global row res0 first)
+    int pitch, res0, own0;
+    const float* xsq;
+    const int* y;
+    const float* alpha;
+    const DevState* st;             // for the sequence number
+    int world, rank;
+    size_t package;                 // bytes per package
+    unsigned char* peer_mail[kMaxPeers];   // base of rank q's mailbox as mapped here (q == rank: local)
+    unsigned int* peer_flag[kMaxPeers];
+};
+
 struct CtlDev {
     DevState* st;
     unsigned long long* keys;   // [2] local selection result of the previous pass
@@ -91,6 +116,7 @@ struct CtlDev {
     const unsigned char* cand;  // [world x cand_stride]
     size_t cand_stride;
     int own0, own_n;            // owned global row range: only the owner installs a new alpha
+    const unsigned int* flags;  // peer-memory exchange: [2 slots][world] arrival flags (null: cand is already complete)
     const float* ext_row_hi;    // optional externally supplied rows (device pointers)
     const float* ext_row_lo;
 };
@@ -103,6 +129,7 @@ cudaError_t launch_select(const float* alpha, const int* y, const float* f, int 
                           unsigned long long* keys, cudaStream_t s);
 cudaError_t launch_control(const CtlDev& a, cudaStream_t s);
 cudaError_t launch_pack(const PackDev& a, cudaStream_t s);
+cudaError_t launch_push(const PushDev* d_push, cudaStream_t s);   // publish the current local selection (initial package)
 cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStream_t s);
 
 }  // namespace dpsvm

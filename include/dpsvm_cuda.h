@@ -297,6 +297,11 @@ int dpsvm_smo_iteration_noalloc(const dpsvm_iteration_args* args, void* stream);
  * (torch.distributed broadcast, a file, MPI ...); every rank then joins. */
 int dpsvm_comm_unique_id(unsigned char id[DPSVM_COMM_ID_BYTES]);
 int dpsvm_comm_init(dpsvm_ctx* ctx, const unsigned char id[DPSVM_COMM_ID_BYTES], int rank, int world);
+/* Which transport the per-iteration exchange uses: 0 = none (single GPU), 1 = NCCL all-gather
+ * captured in the graph, 2 = peer memory (the pass's last CTA stores the candidate package into every
+ * rank's CUDA-IPC-mapped mailbox over NVLink; the control kernel waits on arrival flags). Peer memory
+ * is the default and is chosen only if every rank could map every peer; DPSVM_EXCHANGE=nccl forces 1. */
+int dpsvm_comm_transport(dpsvm_ctx* ctx);
 
 #ifdef __cplusplus
 }

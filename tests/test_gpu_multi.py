@@ -26,7 +26,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, cache, out_dir):
+def _worker(rank, world, port, name, cache, exchange, out_dir):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
@@ -35,10 +35,9 @@ def _worker(rank, world, port, name, cache, out_dir):
     import torch.distributed as dist
     from conftest import load_golden
     from dpsvm_b200 import capi
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
+    os.environ["DPSVM_EXCHANGE"] = exchange
     torch.cuda.set_device(rank)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dist.init_process_group("gloo", init_method="file://" + os.path.join(out_dir, "rdzv"), rank=rank, world_size=world)
     g = load_golden(name)
     n, d = int(g["n"]), int(g["d"])
     size, disp = capi.shard_layout(n, world)
@@ -52,18 +51,19 @@ def _worker(rank, world, port, name, cache, out_dir):
         st = t.train()
         alpha, f, _ = t.download()
         np.savez(os.path.join(out_dir, "r%d.npz" % rank), alpha=alpha, f=f, it=st.num_iter, conv=st.converged,
-                 b=st.b, hits=st.cache_hits, lo=lo)
+                 b=st.b, hits=st.cache_hits, lo=lo, transport=t.comm_transport)
     dist.barrier()
     dist.destroy_process_group()
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("name,cache", [("mnist_512", 0), ("adult_2048", 10), ("odd_d_333x37", 4)])
-def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache):
+@pytest.mark.parametrize("name,cache,exchange", [("mnist_512", 0, "p2p"), ("adult_2048", 10, "p2p"), ("odd_d_333x37", 4, "p2p"),
+                                                 ("mnist_512", 10, "nccl"), ("odd_d_333x37", 0, "nccl")])
+def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache, exchange):
     import torch.multiprocessing as mp
     from dpsvm_b200 import capi
     world = min(_ngpu(), 4 if name == "adult_2048" else 2)
-    mp.spawn(_worker, args=(world, _free_port(), name, cache, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), name, cache, exchange, str(tmp_path)), nprocs=world, join=True)
     g = golden(name)
     with capi.Trainer(int(g["n"]), int(g["d"]), float(g["c"]), float(g["gamma"]), float(g["epsilon"]),
                       max_iter=int(g["max_iter"]), cache_size=cache) as t:
@@ -72,6 +72,7 @@ def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache):
         alpha, f, _ = t.download()
     parts = [np.load(tmp_path / ("r%d.npz" % r)) for r in range(world)]
     for p in parts:
+        assert str(p["transport"]) == exchange      # peer mapping must actually be in use when asked for
         assert int(p["it"]) == st.num_iter and int(p["conv"]) == st.converged and float(p["b"]) == st.b
         assert int(p["hits"]) == st.cache_hits
     assert np.array_equal(np.concatenate([p["alpha"] for p in parts]), alpha)

@@ -26,9 +26,7 @@ def _worker(rank, world, port, iters, out_dir):
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     from dpsvm_b200 import capi, datagen
     from oracle import pyoracle as po
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dist.init_process_group("gloo", init_method="file://" + os.path.join(out_dir, "rdzv"), rank=rank, world_size=world)
     n, d, c, gamma = 301, 24, 10.0, 0.25
     x, y = datagen.mnist_like(n, d, seed=33)
     size, disp = capi.shard_layout(n, world)
