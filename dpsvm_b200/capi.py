@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(HERE, "libdpsvm.so")
 OK = 0
 FLAG_NO_GRAPH = 1
 FLAG_X_SHARD_ONLY = 2
+FLAG_GRAPH_LOOP = 4
 KEY_EMPTY = 0xFFFFFFFFFFFFFFFF
 COMM_ID_BYTES = 128
 

@@ -282,6 +282,7 @@ extern "C" int dpsvm_comm_init(dpsvm_ctx* c, const unsigned char id[DPSVM_COMM_I
     c->comm = s;
     c->world = world;
     c->rank = rank;
+    c->loop_resident = 0;          // the sharded loop runs as the [control, pass] graph
 
     // transport: peer memory unless told otherwise; every rank must agree, so the outcome is voted on
     const char* ex = getenv("DPSVM_EXCHANGE");

@@ -4,6 +4,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <new>
 #include <vector>
@@ -46,6 +47,7 @@ static void free_all(dpsvm_ctx* c)
     cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_st);
     cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
     cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
+    cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru);
     predict_free(c);
     comm_free(c);
     if (c->h_st) cudaFreeHost(c->h_st);
@@ -152,8 +154,96 @@ static int build_graph(dpsvm_ctx* c)
     return rc;
 }
 
+static int init_cache(dpsvm_ctx* c);
+
+// The two loops keep the kernel-row cache's bookkeeping in different structures (recency lists +
+// direct index for the split kernels, a replicated table for the resident loop).  Switching loops
+// mid-run simply empties the cache: results never depend on cache contents.
+static int ensure_cache_path(dpsvm_ctx* c, int path)
+{
+    if (c->cache.lines <= 0 || c->cache_path == path) { c->cache_path = path; return DPSVM_OK; }
+    if (c->cache_path != 0) {
+        int rc = init_cache(c);
+        if (rc != DPSVM_OK) return rc;
+    }
+    c->cache_path = path;
+    return DPSVM_OK;
+}
+
+static int launch_resident_chunk(dpsvm_ctx* c)
+{
+    int rc = ensure_cache_path(c, 2);
+    if (rc != DPSVM_OK) return rc;
+    CU(cudaMemsetAsync(c->d_barrier, 0, sizeof(unsigned int), c->stream));
+    ResidentDev a{};
+    const int off = c->p.shard_start - c->res0;
+    a.x4 = reinterpret_cast<const float4*>(c->d_x + (size_t)off * c->pitch);
+    a.n = c->p.shard_rows;
+    a.pitch4 = c->pitch / 4;
+    a.xsq = c->d_xsq + off;
+    a.y = c->d_y + off;
+    a.alpha = c->d_alpha + off;
+    a.f = c->d_f;
+    a.gamma = c->p.gamma; a.c = c->p.c; a.epsilon = c->p.epsilon;
+    a.max_iter = c->p.max_iter;
+    a.index_base = c->p.shard_start;
+    a.st = c->d_st;
+    a.keys = c->d_keys;
+    a.slots = c->d_slots;
+    a.barrier = c->d_barrier;
+    a.chunk = c->chunk;
+    a.cache_lines = c->cache.lines;
+    a.cache_data = c->cache.data;
+    a.line_stride = c->cache.line_stride;
+    a.lru_key = c->d_lru;
+    a.lru_stamp = c->d_lru + kResCacheLines;
+    a.lru_meta = c->d_lru + 2 * kResCacheLines;
+    static unsigned long long* d_trace = nullptr;
+    const int trace_on = env_int("DPSVM_TRACE", 0);
+    if (trace_on && !d_trace) CU(cudaMalloc(&d_trace, sizeof(unsigned long long) * 4 * 1024));
+    a.trace = trace_on ? d_trace : nullptr;
+    a.trace_iter = env_int("DPSVM_TRACE_ITER", 20);
+    CU(launch_resident(a, variant_for(c, (int)(c->launched_iters & 1)), c->stream));
+    c->launched_iters += c->chunk;
+    if (trace_on && c->launched_iters == (long long)c->chunk * trace_on) {
+        // debugging aid: phase times of one iteration, per CTA (chain | sweep | barrier wait), in us
+        std::vector<unsigned long long> h(4 * 1024);
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaMemcpy(h.data(), d_trace, sizeof(unsigned long long) * 4 * 1024, cudaMemcpyDeviceToHost));
+        const int G = device_sm_count();
+        double mx[3] = {0, 0, 0}, mn[3] = {1e30, 1e30, 1e30}, sum[3] = {0, 0, 0};
+        unsigned long long t_first = ~0ull, t_last = 0;
+        for (int b = 0; b < G; ++b) {
+            for (int k = 0; k < 3; ++k) {
+                const double us = (double)(h[b * 4 + k + 1] - h[b * 4 + k]) * 1e-3;
+                mx[k] = us > mx[k] ? us : mx[k]; mn[k] = us < mn[k] ? us : mn[k]; sum[k] += us;
+            }
+            t_first = h[b * 4] < t_first ? h[b * 4] : t_first;
+            t_last = h[b * 4 + 3] > t_last ? h[b * 4 + 3] : t_last;
+        }
+        if (const char* dump = getenv("DPSVM_TRACE_DUMP")) {
+            if (FILE* fp = fopen(dump, "a")) {
+                for (int b = 0; b < G; ++b)
+                    fprintf(fp, "%d %d %.3f %.3f %.3f\n", a.trace_iter, b, (double)(h[b * 4 + 1] - h[b * 4]) * 1e-3,
+                            (double)(h[b * 4 + 2] - h[b * 4 + 1]) * 1e-3, (double)(h[b * 4 + 3] - h[b * 4 + 2]) * 1e-3);
+                fclose(fp);
+            }
+        }
+        fprintf(stderr, "[dpsvm trace] iteration %d over %d CTAs: chain min/avg/max %.2f/%.2f/%.2f us | sweep %.2f/%.2f/%.2f us | "
+                        "barrier wait %.2f/%.2f/%.2f us | first start -> last release %.2f us\n",
+                a.trace_iter, G, mn[0], sum[0] / G, mx[0], mn[1], sum[1] / G, mx[1], mn[2], sum[2] / G, mx[2],
+                (double)(t_last - t_first) * 1e-3);
+    }
+    return DPSVM_OK;
+}
+
 static int launch_chunk(dpsvm_ctx* c)
 {
+    if (c->loop_resident) return launch_resident_chunk(c);
+    {
+        int rc = ensure_cache_path(c, 1);
+        if (rc != DPSVM_OK) return rc;
+    }
     if (c->p.flags & DPSVM_FLAG_NO_GRAPH) {
         for (int i = 0; i < c->chunk; ++i) {
             int rc = launch_iteration(c, c->stream, i);
@@ -199,6 +289,7 @@ static int init_cache(dpsvm_ctx* c)
     if (k.lines <= 0) return DPSVM_OK;
     CU(cudaMemsetAsync(k.line_of_key, 0xFF, sizeof(int) * (size_t)c->p.num_train_data, c->stream));
     CU(cudaMemsetAsync(k.meta, 0, sizeof(int) * kCacheMetaInts, c->stream));
+    CU(cudaMemsetAsync(c->d_lru, 0, sizeof(int) * (2 * kResCacheLines + 2), c->stream));
     const int minus1[2] = {-1, -1};   // pageable source: staged before the call returns
     CU(cudaMemcpyAsync(k.meta + kCacheHead, minus1, 2 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     return DPSVM_OK;
@@ -215,6 +306,7 @@ static int reset_state(dpsvm_ctx* c)
     if (rc != DPSVM_OK) return rc;
     rc = init_cache(c);
     if (rc != DPSVM_OK) return rc;
+    c->cache_path = 0;
     CU(launch_select(c->d_alpha + off, c->d_y + off, c->d_f, c->p.shard_rows, c->p.c, c->p.shard_start,
                      c->d_keys, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -308,6 +400,13 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     c->variant = env_int("DPSVM_VARIANT", dpsvm_pass_variant(p->shard_rows, c->pitch, 0));
     c->serpentine = env_int("DPSVM_SERPENTINE", 1);
     c->pdl = env_int("DPSVM_PDL", 1);
+    // loop: the resident (persistent cooperative) kernel whenever it applies; DPSVM_FLAG_GRAPH_LOOP or
+    // DPSVM_LOOP=graph keep the [control, pass] CUDA-graph loop (multi-GPU runs always use the graph loop)
+    {
+        const char* lp = getenv("DPSVM_LOOP");
+        const bool want_graph = (p->flags & (DPSVM_FLAG_GRAPH_LOOP | DPSVM_FLAG_NO_GRAPH)) || (lp && strcmp(lp, "graph") == 0);
+        c->loop_resident = (!want_graph && resident_supported(c->pitch / 4, p->cache_size >= 2 ? p->cache_size : 0)) ? 1 : 0;
+    }
     if (c->chunk > 1 && (c->chunk & 1)) c->chunk += 1;   // even chunks keep the direction alternating across launches
     c->world = 1; c->rank = 0;
     // the reference with one line aliases the hi and lo buffers (latent bug, cache.cu:82-105): a
@@ -338,6 +437,9 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     CUC(cudaMalloc(&c->d_ext_rows, sizeof(float) * 2 * (size_t)c->pitch));
     CUC(cudaMalloc(&c->d_keys, 2 * sizeof(unsigned long long)));
     CUC(cudaMalloc(&c->d_st, sizeof(DevState)));
+    CUC(cudaMalloc(&c->d_slots, 2 * 1024 * sizeof(ResSlot)));
+    CUC(cudaMalloc(&c->d_barrier, sizeof(unsigned int)));
+    CUC(cudaMalloc(&c->d_lru, sizeof(int) * (2 * kResCacheLines + 2)));
     CUC(cudaMallocHost(&c->h_st, 2 * sizeof(DevState)));
     CUC(cudaMallocHost(&c->h_keys, 2 * sizeof(unsigned long long)));
     CUC(cudaMallocHost(&c->h_small, 16 * sizeof(int)));
@@ -434,6 +536,10 @@ int dpsvm_step2(dpsvm_ctx* c, int i_hi, int i_lo, float alpha_hi_new, float alph
     if (!hi_res || !lo_res)
         return fail(DPSVM_ERR_STATE, "dpsvm_step2: non-resident rows need the fused multi-GPU loop (dpsvm_train)");
     CU(cudaSetDevice(c->device));
+    {
+        int rc = ensure_cache_path(c, 1);
+        if (rc != DPSVM_OK) return rc;
+    }
     CtlDev a = make_ctl_args(c);
     a.directed = 1; a.dir_i_hi = i_hi; a.dir_i_lo = i_lo; a.dir_a_hi = alpha_hi_new; a.dir_a_lo = alpha_lo_new;
     const int d = c->p.num_attributes;
@@ -565,7 +671,9 @@ int dpsvm_cache_lookup(dpsvm_ctx* c, int key, float** d_line, int* hit)
     if (key < 0 || key >= c->p.num_train_data) return fail(DPSVM_ERR_INVALID, "dpsvm_cache_lookup: key out of range");
     CU(cudaSetDevice(c->device));
     int line = -1;
-    int rc = cache_lookup_host(c, key, &line, hit);
+    int rc = ensure_cache_path(c, 1);
+    if (rc != DPSVM_OK) return rc;
+    rc = cache_lookup_host(c, key, &line, hit);
     if (rc != DPSVM_OK) return rc;
     *d_line = c->cache.data + (size_t)line * c->cache.line_stride;
     return DPSVM_OK;

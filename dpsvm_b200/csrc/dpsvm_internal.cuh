@@ -35,6 +35,14 @@ struct dpsvm_ctx {
 
     dpsvm::CacheDev cache{};
 
+    // resident loop (smo_resident.cu)
+    int loop_resident = 0;       // 1: the persistent cooperative kernel runs the iterations
+    dpsvm::ResSlot* d_slots = nullptr;
+    unsigned int* d_barrier = nullptr;
+    int* d_lru = nullptr;        // [kResCacheLines keys][kResCacheLines stamps][2 meta]
+    int cache_path = 0;          // which loop last owned the kernel-row cache: 0 none, 1 graph/split, 2 resident
+    long long launched_iters = 0;
+
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t gexec = nullptr;
 

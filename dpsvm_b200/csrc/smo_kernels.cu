@@ -10,52 +10,12 @@
 //                        svmTrain.cu:142-156,487-494 / cache.cu:62-105 (cache lookup, alpha install)
 //
 // The pass is HBM-bound (2 dot products per row = GEMM with N=2, ~1 flop/byte): no tensor cores.
-#include "smo_kernels.cuh"
+#include "smo_device.cuh"
 
 #include <math.h>
 
 namespace dpsvm {
 
-// ------------------------------------------------------------------------------------------------
-// small PTX helpers
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float4 ldg_stream4(const float4* p)
-{
-    // X is read exactly once per pass: keep it out of L1.
-    float4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-// TMA bulk copy global -> shared (1-D, no tensor map): bytes % 16 == 0, both sides 16 B aligned.
-__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
-__device__ __forceinline__ unsigned long long umin64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
 
 // Stage the two selected rows in shared memory with TMA bulk copies and zero the tail up to `cap4`.
 __device__ __forceinline__ void stage_selected_rows(float4* s_hi, float4* s_lo, const float4* g_hi, const float4* g_lo,
@@ -108,16 +68,6 @@ __device__ __forceinline__ void publish_keys(unsigned long long best_up, unsigne
 // the final local keys and stores it into slot (seq & 1) of every rank's mailbox -- stores to
 // CUDA-IPC-mapped peer memory travel over NVLink -- then raises this rank's flag there.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v)
-{
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p)
-{
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 
 __device__ void pack_and_push(const PushDev& p)
 {
@@ -229,19 +179,6 @@ __device__ __forceinline__ void pass_both_hit(const PassScalars& sc, const PassD
 //   a.reverse: sweep the units back to front (serpentine order across consecutive iterations: the
 //   tail of the previous pass is what L2 still holds).
 // ------------------------------------------------------------------------------------------------
-template <bool HINT>
-__device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
-{
-    float4 v;
-    if (HINT) {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
-                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(pol));
-    } else {
-        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    }
-    return v;
-}
 
 template <int LPR, int ITERS, bool HINT>
 __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_kernel(const PassDev a)

@@ -121,6 +121,50 @@ struct CtlDev {
     const float* ext_row_lo;
 };
 
+// ---- resident loop (smo_resident.cu): persistent cooperative kernel, one CTA per SM ----
+constexpr int kResThreads = 512;
+constexpr int kResCacheLines = 64;      // largest kernel-row cache whose LRU table is replicated per CTA
+
+struct ResSlot {                        // what a CTA publishes after its sweep
+    unsigned long long key_up, key_low; // block-best packed keys
+    float a_up, a_low;                  // alpha of those two rows
+    int pad[2];
+};
+static_assert(sizeof(ResSlot) == 32, "ResSlot is 32 bytes");
+
+struct ResidentDev {
+    const float4* x4;           // [n x pitch4] owned rows
+    int n, pitch4;
+    const float* xsq;           // [n]
+    const int* y;               // [n]
+    float* alpha;               // [n]
+    float* f;                   // [n]
+    float gamma, c, epsilon;
+    int max_iter, index_base;
+    DevState* st;
+    unsigned long long* keys;   // [2] selection in (launch) / out (exit)
+    ResSlot* slots;             // [2][grid]
+    unsigned int* barrier;      // arrival counter, zero at launch
+    int chunk;                  // at most this many iterations per launch
+    // kernel-row cache (cache_lines <= kResCacheLines): replicated LRU table, lines in global memory
+    int cache_lines;
+    float* cache_data;
+    size_t line_stride;
+    int* lru_key;               // [cache_lines]
+    int* lru_stamp;             // [cache_lines]
+    int* lru_meta;              // [2] size, clock
+    // filled by the launcher
+    int res_units;              // units of X each CTA keeps in shared memory
+    int pin_units;              // streamed units per CTA loaded L2::evict_last
+    int stream_evict_first;
+    int parity0;                // sweep direction of the launch's first iteration
+    unsigned long long* trace;  // optional [grid][4] globaltimer stamps of iteration trace_iter (DPSVM_TRACE)
+    int trace_iter;
+};
+
+bool resident_supported(int pitch4, int cache_lines);
+cudaError_t launch_resident(const ResidentDev& a, int variant, cudaStream_t s);
+
 int device_sm_count();
 cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s);
 cudaError_t launch_row_norms(const float* x, int n, int pitch, float* out, cudaStream_t s);

@@ -160,6 +160,8 @@ typedef struct {
 #define DPSVM_FLAG_NONE 0
 #define DPSVM_FLAG_NO_GRAPH 1        /* launch kernels one by one instead of through a CUDA graph */
 #define DPSVM_FLAG_X_SHARD_ONLY 2    /* dpsvm_upload receives / keeps only the owned rows of X */
+#define DPSVM_FLAG_GRAPH_LOOP 4      /* run the loop as a CUDA graph of [control, pass] kernel pairs instead of the
+                                        resident (persistent, cooperative) kernel; results are identical */
 
 int dpsvm_create(const dpsvm_params* params, dpsvm_ctx** out);
 int dpsvm_destroy(dpsvm_ctx* ctx);

@@ -444,3 +444,46 @@ def test_full_shape_properties(torch, oracle):
             assert (st.i_hi, st.i_lo) == tuple(r.trace_idx[k])
         alpha, f, _ = t.download()
     assert np.abs(alpha - r.alpha).max() < 1e-4 and np.abs(f - r.f).max() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------
+# the two loops: resident (persistent cooperative kernel, default) vs CUDA graph of [control, pass]
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,cache", [("mnist_512", 0), ("mnist_512", 10), ("adult_2048", 4), ("odd_d_333x37", 0),
+                                        ("dups_96x16", 2), ("tiny_3x5", 0), ("mnist_1024_tight", 64)])
+def test_resident_and_graph_loops_are_bit_identical(golden, name, cache):
+    g = golden(name)
+    out = []
+    for flags in (0, capi.FLAG_GRAPH_LOOP):
+        with _trainer(g, cache_size=cache, flags=flags) as t:
+            st = t.train()
+            a, f, _ = t.download()
+            rv, keys = t.step1()
+            out.append((st.num_iter, st.converged, st.b_hi, st.b_lo, st.cache_hits, st.cache_lookups, a, f, keys))
+    r, q = out
+    assert r[:6] == q[:6]
+    assert np.array_equal(r[6], q[6]) and np.array_equal(r[7], q[7]) and r[8] == q[8]
+
+
+def test_loops_can_be_mixed_with_the_dropin_steps(golden):
+    """resident chunks, then host-directed train_step2 iterations (split kernels), then resident again:
+    the kernel-row cache is emptied at each switch, results are those of an uninterrupted run."""
+    g = golden("mnist_512")
+    c = float(g["c"])
+    with _trainer(g, cache_size=10) as t:
+        st = t.train(57)
+        rv, _ = t.step1()
+        alpha, _, _ = t.download()
+        i_hi, i_lo, b_hi, b_lo = capi.merge_candidates(rv)
+        with _trainer(g, cache_size=0, flags=capi.FLAG_GRAPH_LOOP) as ref:
+            ref.train(58)
+            a_ref58, f_ref58, _ = ref.download()
+            st_ref = ref.train(30)
+            a_ref88, f_ref88, _ = ref.download()
+        # iteration 58 by hand through the drop-in API, with the device's own eta
+        t2 = t.train(1)
+        a58, f58, _ = t.download()
+        assert np.array_equal(a58, a_ref58) and np.array_equal(f58, f_ref58)
+        t.step2(t2.i_hi, t2.i_lo, float(a58[t2.i_hi]), float(a58[t2.i_lo]))      # a no-change directed step (delta = 0)
+        a58b, f58b, _ = t.download()
+        assert np.array_equal(a58b, a58) and np.allclose(f58b, f58, atol=0)
