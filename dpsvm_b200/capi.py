@@ -69,7 +69,7 @@ EXPORTS = [
     "dpsvm_pitch_for", "dpsvm_pass_variant", "dpsvm_pack_key_up", "dpsvm_pack_key_low", "dpsvm_unpack_key_up", "dpsvm_unpack_key_low",
     "dpsvm_row_norms", "dpsvm_init_state", "dpsvm_select", "dpsvm_smo_pass", "dpsvm_create", "dpsvm_destroy",
     "dpsvm_upload", "dpsvm_upload_device", "dpsvm_reset", "dpsvm_step1", "dpsvm_step2", "dpsvm_train",
-    "dpsvm_train_async", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
+    "dpsvm_train_async", "dpsvm_loop_info", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
     "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init", "dpsvm_comm_transport", "dpsvm_smo_iteration_noalloc",
 ]
 
@@ -107,6 +107,7 @@ def lib():
         L.dpsvm_train.argtypes = [C.c_void_p, C.c_int, C.POINTER(TrainStatus)]
         L.dpsvm_train_async.argtypes = [C.c_void_p, C.c_int]
         L.dpsvm_sync.argtypes = [C.c_void_p, C.POINTER(TrainStatus)]
+        L.dpsvm_loop_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.dpsvm_stream.restype = C.c_void_p
         L.dpsvm_stream.argtypes = [C.c_void_p]
         L.dpsvm_download.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -292,6 +293,12 @@ class Trainer:
         st = TrainStatus()
         check(lib().dpsvm_sync(self._h, C.byref(st)))
         return st
+
+    def loop_info(self):
+        """(resident: bool, chunk: int) -- see dpsvm_loop_info."""
+        r, k = C.c_int(), C.c_int()
+        check(lib().dpsvm_loop_info(self._h, C.byref(r), C.byref(k)))
+        return bool(r.value), k.value
 
     @property
     def stream(self):

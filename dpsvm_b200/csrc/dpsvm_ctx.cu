@@ -592,6 +592,14 @@ int dpsvm_sync(dpsvm_ctx* c, dpsvm_train_status* status)
 
 void* dpsvm_stream(dpsvm_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
+int dpsvm_loop_info(dpsvm_ctx* c, int* resident, int* chunk)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_loop_info: null context");
+    if (resident) *resident = (c->loop_resident && c->world == 1) ? 1 : 0;
+    if (chunk) *chunk = c->chunk;
+    return DPSVM_OK;
+}
+
 int dpsvm_train(dpsvm_ctx* c, int max_new_iter, dpsvm_train_status* status)
 {
     if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_train: null context");

@@ -214,6 +214,10 @@ int dpsvm_train(dpsvm_ctx* ctx, int max_new_iter, dpsvm_train_status* status);
 /* Run exactly `iters` iterations asynchronously on the context's stream (no host sync, no early
  * exit on the host side; iterations after convergence are no-ops on the device).  For timing. */
 int dpsvm_train_async(dpsvm_ctx* ctx, int iters);
+/* How the loop runs on this context: *resident = 1 for the persistent cooperative kernel (one launch =
+ * up to *chunk iterations), 0 for the CUDA graph of [control, pass] pairs (one graph launch = *chunk
+ * iterations).  Either output may be NULL. */
+int dpsvm_loop_info(dpsvm_ctx* ctx, int* resident, int* chunk);
 int dpsvm_sync(dpsvm_ctx* ctx, dpsvm_train_status* status);
 void* dpsvm_stream(dpsvm_ctx* ctx);
 
