@@ -17,7 +17,22 @@ HOST_SRCS := $(HOST)/svmTrain.cpp $(HOST)/parse.cpp $(HOST)/model_io.cpp
 HOST_LIB  := dpsvm_b200/libdpsvm_host.so
 CLI       := dpsvm_b200/svmTrain
 
-all: lib host oracle
+REF       ?= /root/reference
+
+all: lib host oracle $(if $(wildcard $(REF)/svmTrainMain.cpp),dropin refgpu,)
+
+# drop-in proof: the UNMODIFIED reference driver linked against this repo's SvmTrain (tools/dropin_check.sh)
+dropin: host
+	REF=$(REF) tools/dropin_check.sh
+
+# the reference's own GPU path (cuBLAS gemv + Thrust) rebuilt for sm_100a from the sources where
+# they lie, as a comparison binary for the same B200 (oracle/_ref is git-ignored and travels to the GPU box).
+# -std=c++14: `beta` at svmTrain.cu:38 collides with std::beta under C++17; -include thrust/remove.h: svmTrain.cu:597.
+refgpu: oracle/_ref/svmTrain_refgpu
+oracle/_ref/svmTrain_refgpu: $(REF)/svmTrain.cu $(REF)/cache.cu $(REF)/parse.cpp $(REF)/svmTrainMain.cpp tools/dropin/mpi.h oracle/cblas_shim/cblas.h
+	@mkdir -p oracle/_ref
+	$(NVCC) $(ARCH) -x cu -O3 -std=c++14 -w -Ioracle/cblas_shim -Itools/dropin -include thrust/remove.h -o $@ \
+	    $(REF)/svmTrain.cu $(REF)/cache.cu $(REF)/parse.cpp $(REF)/svmTrainMain.cpp -lcublas
 
 lib: $(LIB)
 
@@ -43,4 +58,4 @@ clean:
 	rm -rf $(OBJDIR) $(LIB) $(HOST_LIB) $(CLI)
 	$(MAKE) -C oracle clean
 
-.PHONY: all lib host oracle clean
+.PHONY: all lib host oracle clean dropin refgpu
