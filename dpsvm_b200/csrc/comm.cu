@@ -130,6 +130,7 @@ int try_setup_p2p(dpsvm_ctx* c, CommState* s)
     PushDev h{};
     h.counter = s->d_counter;
     h.keys = c->d_keys;
+    h.keys_copy = c->d_keys_copy;
     h.x = c->d_x;
     h.pitch = c->pitch;
     h.res0 = c->res0;
@@ -195,6 +196,18 @@ int comm_after_select(dpsvm_ctx* c)
     return DPSVM_OK;
 }
 
+bool comm_fill_resident(dpsvm_ctx* c, ResidentDev* a)
+{
+    CommState* s = static_cast<CommState*>(c->comm);
+    if (!s || !s->p2p) return false;
+    a->world = c->world;
+    a->push = s->d_push;
+    a->mail = s->d_box + kFlagBytes;
+    a->flags = reinterpret_cast<const unsigned int*>(s->d_box);
+    a->package = s->package;
+    return true;
+}
+
 // One iteration of the sharded loop.
 int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t stream, int variant)
 {
@@ -212,6 +225,7 @@ int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t stream, int variant)
     } else {
         PackDev p{};
         p.keys = c->d_keys;
+        p.keys_copy = c->d_keys_copy;
         p.x = c->d_x;
         p.pitch = c->pitch;
         p.res0 = c->res0;
@@ -282,7 +296,7 @@ extern "C" int dpsvm_comm_init(dpsvm_ctx* c, const unsigned char id[DPSVM_COMM_I
     c->comm = s;
     c->world = world;
     c->rank = rank;
-    c->loop_resident = 0;          // the sharded loop runs as the [control, pass] graph
+    // (the resident loop runs multi-GPU only over the peer-memory exchange; decided below)
 
     // transport: peer memory unless told otherwise; every rank must agree, so the outcome is voted on
     const char* ex = getenv("DPSVM_EXCHANGE");

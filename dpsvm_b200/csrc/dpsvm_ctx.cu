@@ -44,7 +44,7 @@ static void free_all(dpsvm_ctx* c)
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
     if (c->graph) cudaGraphDestroy(c->graph);
     cudaFree(c->d_x); cudaFree(c->d_xsq); cudaFree(c->d_y); cudaFree(c->d_alpha); cudaFree(c->d_f);
-    cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_st);
+    cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_keys_copy); cudaFree(c->d_st);
     cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
     cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
     cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru);
@@ -198,34 +198,36 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.lru_key = c->d_lru;
     a.lru_stamp = c->d_lru + kResCacheLines;
     a.lru_meta = c->d_lru + 2 * kResCacheLines;
+    a.world = 1;
+    if (c->world > 1 && !comm_fill_resident(c, &a)) return fail(DPSVM_ERR_STATE, "resident loop needs the peer-memory exchange");
     static unsigned long long* d_trace = nullptr;
     const int trace_on = env_int("DPSVM_TRACE", 0);
-    if (trace_on && !d_trace) CU(cudaMalloc(&d_trace, sizeof(unsigned long long) * 4 * 1024));
+    if (trace_on && !d_trace) { CU(cudaMalloc(&d_trace, sizeof(unsigned long long) * 8 * 1024)); CU(cudaMemset(d_trace, 0, sizeof(unsigned long long) * 8 * 1024)); }
     a.trace = trace_on ? d_trace : nullptr;
     a.trace_iter = env_int("DPSVM_TRACE_ITER", 20);
     CU(launch_resident(a, variant_for(c, (int)(c->launched_iters & 1)), c->stream));
     c->launched_iters += c->chunk;
     if (trace_on && c->launched_iters == (long long)c->chunk * trace_on) {
         // debugging aid: phase times of one iteration, per CTA (chain | sweep | barrier wait), in us
-        std::vector<unsigned long long> h(4 * 1024);
+        std::vector<unsigned long long> h(8 * 1024);
         CU(cudaStreamSynchronize(c->stream));
-        CU(cudaMemcpy(h.data(), d_trace, sizeof(unsigned long long) * 4 * 1024, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(h.data(), d_trace, sizeof(unsigned long long) * 8 * 1024, cudaMemcpyDeviceToHost));
         const int G = device_sm_count();
         double mx[3] = {0, 0, 0}, mn[3] = {1e30, 1e30, 1e30}, sum[3] = {0, 0, 0};
         unsigned long long t_first = ~0ull, t_last = 0;
         for (int b = 0; b < G; ++b) {
             for (int k = 0; k < 3; ++k) {
-                const double us = (double)(h[b * 4 + k + 1] - h[b * 4 + k]) * 1e-3;
+                const double us = (double)(h[b * 8 + k + 1] - h[b * 8 + k]) * 1e-3;
                 mx[k] = us > mx[k] ? us : mx[k]; mn[k] = us < mn[k] ? us : mn[k]; sum[k] += us;
             }
-            t_first = h[b * 4] < t_first ? h[b * 4] : t_first;
-            t_last = h[b * 4 + 3] > t_last ? h[b * 4 + 3] : t_last;
+            t_first = h[b * 8] < t_first ? h[b * 8] : t_first;
+            t_last = h[b * 8 + 3] > t_last ? h[b * 8 + 3] : t_last;
         }
         if (const char* dump = getenv("DPSVM_TRACE_DUMP")) {
             if (FILE* fp = fopen(dump, "a")) {
                 for (int b = 0; b < G; ++b)
-                    fprintf(fp, "%d %d %.3f %.3f %.3f\n", a.trace_iter, b, (double)(h[b * 4 + 1] - h[b * 4]) * 1e-3,
-                            (double)(h[b * 4 + 2] - h[b * 4 + 1]) * 1e-3, (double)(h[b * 4 + 3] - h[b * 4 + 2]) * 1e-3);
+                    fprintf(fp, "%d %d %.3f %.3f %.3f\n", a.trace_iter, b, (double)(h[b * 8 + 1] - h[b * 8]) * 1e-3,
+                            (double)(h[b * 8 + 2] - h[b * 8 + 1]) * 1e-3, (double)(h[b * 8 + 3] - h[b * 8 + 2]) * 1e-3);
                 fclose(fp);
             }
         }
@@ -233,13 +235,17 @@ static int launch_resident_chunk(dpsvm_ctx* c)
                         "barrier wait %.2f/%.2f/%.2f us | first start -> last release %.2f us\n",
                 a.trace_iter, G, mn[0], sum[0] / G, mx[0], mn[1], sum[1] / G, mx[1], mn[2], sum[2] / G, mx[2],
                 (double)(t_last - t_first) * 1e-3);
+        if (c->world > 1)
+            fprintf(stderr, "[dpsvm trace] rank %d CTA0: local merge %.2f us after barrier | push %.2f us | remote wait+merge (CTA0 / CTA1) %.2f / %.2f us\n",
+                    c->rank, (double)(h[4] - h[3]) * 1e-3, (double)(h[5] - h[4]) * 1e-3, (double)(h[6] - h[5]) * 1e-3,
+                    (double)(h[8 + 6] - h[8 + 5]) * 1e-3);
     }
     return DPSVM_OK;
 }
 
 static int launch_chunk(dpsvm_ctx* c)
 {
-    if (c->loop_resident) return launch_resident_chunk(c);
+    if (c->loop_resident && (c->world == 1 || c->exchange_p2p)) return launch_resident_chunk(c);
     {
         int rc = ensure_cache_path(c, 1);
         if (rc != DPSVM_OK) return rc;
@@ -309,6 +315,7 @@ static int reset_state(dpsvm_ctx* c)
     c->cache_path = 0;
     CU(launch_select(c->d_alpha + off, c->d_y + off, c->d_f, c->p.shard_rows, c->p.c, c->p.shard_start,
                      c->d_keys, c->stream));
+    CU(cudaMemcpyAsync(c->d_keys_copy, c->d_keys, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->target_iter = 0;
     if (c->world > 1) return comm_after_select(c);
@@ -436,6 +443,7 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     CUC(cudaMalloc(&c->d_sel_rows, sizeof(float) * 2 * (size_t)c->pitch));
     CUC(cudaMalloc(&c->d_ext_rows, sizeof(float) * 2 * (size_t)c->pitch));
     CUC(cudaMalloc(&c->d_keys, 2 * sizeof(unsigned long long)));
+    CUC(cudaMalloc(&c->d_keys_copy, 2 * sizeof(unsigned long long)));
     CUC(cudaMalloc(&c->d_st, sizeof(DevState)));
     CUC(cudaMalloc(&c->d_slots, 2 * 1024 * sizeof(ResSlot)));
     CUC(cudaMalloc(&c->d_barrier, sizeof(unsigned int)));
@@ -509,7 +517,9 @@ int dpsvm_step1(dpsvm_ctx* c, float rv[4], uint64_t keys[2])
 {
     if (!c || !rv) return fail(DPSVM_ERR_INVALID, "dpsvm_step1: null argument");
     if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_step1 before dpsvm_upload");
-    CU(cudaMemcpyAsync(c->h_keys, c->d_keys, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    // multi-GPU: the exchange consumes the live keys; the last published local selection is kept aside
+    CU(cudaMemcpyAsync(c->h_keys, c->world > 1 ? c->d_keys_copy : c->d_keys, 2 * sizeof(unsigned long long),
+                       cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     float f_hi, f_lo; int32_t i_hi, i_lo;
     unpack_key_up(c->h_keys[0], &f_hi, &i_hi);
@@ -595,7 +605,7 @@ void* dpsvm_stream(dpsvm_ctx* c) { return c ? (void*)c->stream : nullptr; }
 int dpsvm_loop_info(dpsvm_ctx* c, int* resident, int* chunk)
 {
     if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_loop_info: null context");
-    if (resident) *resident = (c->loop_resident && c->world == 1) ? 1 : 0;
+    if (resident) *resident = (c->loop_resident && (c->world == 1 || c->exchange_p2p)) ? 1 : 0;
     if (chunk) *chunk = c->chunk;
     return DPSVM_OK;
 }

@@ -28,6 +28,7 @@ struct dpsvm_ctx {
     float* d_sel_rows = nullptr; // [2 x pitch] rows of the current pair, read by the pass
     float* d_ext_rows = nullptr; // [2 x pitch] rows supplied by the host (step2)
     unsigned long long* d_keys = nullptr;   // [2]
+    unsigned long long* d_keys_copy = nullptr;   // [2] multi-GPU: last published local selection (train_step1)
     dpsvm::DevState* d_st = nullptr;
     dpsvm::DevState* h_st = nullptr;        // pinned, 2 slots
     unsigned long long* h_keys = nullptr;   // pinned
@@ -70,5 +71,6 @@ void predict_free(dpsvm_ctx* c);
 void comm_free(dpsvm_ctx* c);
 int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s, int variant);
 int comm_after_select(dpsvm_ctx* c);
+bool comm_fill_resident(dpsvm_ctx* c, ResidentDev* a);   // false: this exchange cannot run inside the resident loop
 
 }  // namespace dpsvm

@@ -71,4 +71,55 @@ __device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
     return v;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Peer-memory candidate exchange (multi-GPU).  Runs in ONE block: builds this rank's package from
+// its local selection and stores it into slot (seq & 1) of every rank's mailbox -- stores to
+// CUDA-IPC-mapped peer memory travel over NVLink -- then raises this rank's flag there to seq + 1.
+// have_alpha: the caller already holds the alpha of the two candidate rows (resident loop); else
+// they are read from global memory.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void push_package(const PushDev& p, unsigned long long k_up, unsigned long long k_low,
+                                             float a_up, float a_low, bool have_alpha, unsigned int seq)
+{
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const unsigned int slot = seq & 1u;
+    float f_dummy;
+    int i_hi = p.own0, i_lo = p.own0;      // an empty set still ships a valid row (the first owned one), so that the
+                                           // reference's "index 0, +-1e9" default (svmTrainMain.cpp:249-252) stays defined
+    if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_hi);
+    if (k_low != DPSVM_KEY_EMPTY) unpack_key_low(k_low, &f_dummy, &i_lo);
+    const int r_hi = i_hi - p.res0, r_lo = i_lo - p.res0;
+    CandHeader h;
+    h.key_up = k_up; h.key_low = k_low;
+    h.a_hi = (have_alpha && k_up != DPSVM_KEY_EMPTY) ? a_up : __ldcg(p.alpha + r_hi);
+    h.a_lo = (have_alpha && k_low != DPSVM_KEY_EMPTY) ? a_low : __ldcg(p.alpha + r_lo);
+    h.y_hi = __ldg(p.y + r_hi); h.y_lo = __ldg(p.y + r_lo);
+    h.xsq_hi = __ldg(p.xsq + r_hi); h.xsq_lo = __ldg(p.xsq + r_lo);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) h.pad[i] = 0;
+    const float4* src_hi = reinterpret_cast<const float4*>(p.x + (size_t)r_hi * p.pitch);
+    const float4* src_lo = reinterpret_cast<const float4*>(p.x + (size_t)r_lo * p.pitch);
+    const int pitch4 = p.pitch / 4;
+    const size_t slot_off = ((size_t)slot * p.world + p.rank) * p.package;
+    // each thread keeps its share of the two rows in registers and stores it to every peer
+    for (int i = tid; i < 2 * pitch4; i += nthr) {
+        const float4 v = (i < pitch4) ? __ldg(src_hi + i) : __ldg(src_lo + (i - pitch4));
+        for (int q = 0; q < p.world; ++q) {
+            float4* dst = reinterpret_cast<float4*>(p.peer_mail[q] + slot_off + sizeof(CandHeader));
+            dst[i] = v;
+        }
+    }
+    if (tid < p.world) {
+        const uint4* hs = reinterpret_cast<const uint4*>(&h);
+        uint4* dst = reinterpret_cast<uint4*>(p.peer_mail[tid] + slot_off);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dst[i] = hs[i];
+    }
+    // No per-thread system fence: the CTA barrier orders every thread's package stores before the flag
+    // stores below, and st.release.sys is cumulative over what happens-before it (PTX memory model), so
+    // a peer that acquires the flag sees the whole package.  (512 system fences cost 6-7 us here.)
+    __syncthreads();
+    if (tid < p.world) st_release_sys_u32(p.peer_flag[tid] + slot * p.world + p.rank, seq + 1u);
+}
+
 }  // namespace dpsvm

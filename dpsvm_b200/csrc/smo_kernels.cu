@@ -71,45 +71,14 @@ __device__ __forceinline__ void publish_keys(unsigned long long best_up, unsigne
 
 __device__ void pack_and_push(const PushDev& p)
 {
-    const int tid = threadIdx.x, nthr = blockDim.x;
     // final keys of this pass: every CTA fenced after its atomicMin and before taking its ticket
     const unsigned long long k_up = __ldcg(p.keys), k_low = __ldcg(p.keys + 1);
     const unsigned int seq = (unsigned int)__ldcg(&p.st->num_iter);
-    const unsigned int slot = seq & 1u;
-    float f_dummy;
-    int i_hi = p.own0, i_lo = p.own0;      // an empty set still ships a valid row (see smo_pack_kernel)
-    if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_hi);
-    if (k_low != DPSVM_KEY_EMPTY) unpack_key_low(k_low, &f_dummy, &i_lo);
-    const int r_hi = i_hi - p.res0, r_lo = i_lo - p.res0;
-    CandHeader h;
-    h.key_up = k_up; h.key_low = k_low;
-    h.a_hi = __ldcg(p.alpha + r_hi); h.a_lo = __ldcg(p.alpha + r_lo);
-    h.y_hi = __ldg(p.y + r_hi); h.y_lo = __ldg(p.y + r_lo);
-    h.xsq_hi = __ldg(p.xsq + r_hi); h.xsq_lo = __ldg(p.xsq + r_lo);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) h.pad[i] = 0;
-    const float4* src_hi = reinterpret_cast<const float4*>(p.x + (size_t)r_hi * p.pitch);
-    const float4* src_lo = reinterpret_cast<const float4*>(p.x + (size_t)r_lo * p.pitch);
-    const int pitch4 = p.pitch / 4;
-    const size_t slot_off = ((size_t)slot * p.world + p.rank) * p.package;
-    // each thread keeps its share of the two rows in registers and stores it to every peer
-    for (int i = tid; i < 2 * pitch4; i += nthr) {
-        const float4 v = (i < pitch4) ? __ldg(src_hi + i) : __ldg(src_lo + (i - pitch4));
-        for (int q = 0; q < p.world; ++q) {
-            float4* dst = reinterpret_cast<float4*>(p.peer_mail[q] + slot_off + sizeof(CandHeader));
-            dst[i] = v;
-        }
+    push_package(p, k_up, k_low, 0.f, 0.f, false, seq);
+    if (threadIdx.x == 0) {
+        p.keys_copy[0] = k_up; p.keys_copy[1] = k_low;      // what train_step1 reports for this rank
+        p.keys[0] = DPSVM_KEY_EMPTY; p.keys[1] = DPSVM_KEY_EMPTY;
     }
-    if (tid < p.world) {
-        const uint4* hs = reinterpret_cast<const uint4*>(&h);
-        uint4* dst = reinterpret_cast<uint4*>(p.peer_mail[tid] + slot_off);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) dst[i] = hs[i];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (tid < p.world) st_release_sys_u32(p.peer_flag[tid] + slot * p.world + p.rank, seq + 1u);
-    if (tid == 0) { p.keys[0] = DPSVM_KEY_EMPTY; p.keys[1] = DPSVM_KEY_EMPTY; }
 }
 
 // After publish_keys: the last CTA of the pass to get here publishes the candidates.
@@ -737,7 +706,10 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_pack_kernel(const PackDev 
         h->xsq_hi = a.xsq[r_hi]; h->xsq_lo = a.xsq[r_lo];
     }
     __syncthreads();
-    if (tid == 0) { a.keys[0] = DPSVM_KEY_EMPTY; a.keys[1] = DPSVM_KEY_EMPTY; }
+    if (tid == 0) {
+        a.keys_copy[0] = k_up; a.keys_copy[1] = k_low;
+        a.keys[0] = DPSVM_KEY_EMPTY; a.keys[1] = DPSVM_KEY_EMPTY;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

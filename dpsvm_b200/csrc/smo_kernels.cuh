@@ -64,6 +64,7 @@ inline size_t cand_package_bytes(int pitch) { return sizeof(CandHeader) + 2 * si
 
 struct PackDev {
     unsigned long long* keys;   // [2] local selection; reset to empty by the pack kernel
+    unsigned long long* keys_copy;   // [2] receives what was packed (train_step1 reads it)
     const float* x;             // resident rows (global row res0 first)
     int pitch, res0, own0;      // own0 = first owned global row (fallback candidate when a set is empty)
     const float* xsq;
@@ -82,6 +83,7 @@ constexpr int kMaxPeers = 16;
 struct PushDev {
     unsigned int* counter;          // CTAs of the current pass that have finished
     unsigned long long* keys;       // [2] local selection; reset to empty after packing
+    unsigned long long* keys_copy;  // [2] the last published local selection (what train_step1 reports)
     const float* x;                 // resident rows (global row res0 first)
     int pitch, res0, own0;
     const float* xsq;
@@ -158,6 +160,12 @@ struct ResidentDev {
     int pin_units;              // streamed units per CTA loaded L2::evict_last
     int stream_evict_first;
     int parity0;                // sweep direction of the launch's first iteration
+    // multi-GPU (world > 1): the pair comes from the peer-memory mailbox (see PushDev); CTA 0 publishes
+    int world;
+    const PushDev* push;
+    const unsigned char* mail;  // local mailbox [2][world][package]
+    const unsigned int* flags;  // local arrival flags [2][world]
+    size_t package;
     unsigned long long* trace;  // optional [grid][4] globaltimer stamps of iteration trace_iter (DPSVM_TRACE)
     int trace_iter;
 };

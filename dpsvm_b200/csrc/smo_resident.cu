@@ -152,10 +152,60 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     const int res_units = min(u1 - u0, a.res_units);   // units kept in shared memory
     const int us0 = u0 + res_units;                    // first streamed unit
 
-    // initial pair: the selection left in the global keys by setup / the previous launch
-    int i_hi, i_lo;
-    float b_hi, b_lo, a_hi_old, a_lo_old;
-    {
+    // the pair of the coming iteration (uniform over the CTA, identical in every CTA and every rank)
+    int i_hi = 0, i_lo = 0;
+    float b_hi = 0.f, b_lo = 0.f, a_hi_old = 0.f, a_lo_old = 0.f;
+    // multi-GPU: scalars and rows of the pair come from the gathered candidate packages
+    int m_y_hi = 0, m_y_lo = 0;
+    float m_xsq_hi = 0.f, m_xsq_lo = 0.f;
+    const float4* m_src_hi = nullptr;
+    const float4* m_src_lo = nullptr;
+
+    // Multi-GPU: wait until every rank's package number `seq` has landed in slot (seq & 1) of the local
+    // mailbox, then merge them exactly as the control kernel does (svmTrainMain.cpp:255-274): the minimum
+    // packed key is argmin f / argmax f with the lowest GLOBAL index among equal values.
+    auto acquire_remote = [&](unsigned int seq) -> bool {
+        if (tid == 0) s_flag = 1;
+        __syncthreads();
+        if (tid < a.world) {
+            const unsigned int want = seq + 1u;
+            const unsigned int* fl = a.flags + (size_t)(seq & 1u) * a.world + tid;
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            unsigned int spins = 0;
+            while (ld_acquire_sys_u32(fl) != want) {
+                if ((++spins & 0xFFu) == 0) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > 4000000000ull) { s_flag = 0; break; }
+                }
+            }
+        }
+        __syncthreads();
+        if (!s_flag) return false;
+        const unsigned char* cand = a.mail + (size_t)(seq & 1u) * a.world * a.package;
+        unsigned long long g_up = DPSVM_KEY_EMPTY, g_low = DPSVM_KEY_EMPTY;
+        int w_up = 0, w_low = 0;
+        for (int r = 0; r < a.world; ++r) {
+            const CandHeader* h = reinterpret_cast<const CandHeader*>(cand + (size_t)r * a.package);
+            const unsigned long long u = __ldcg(&h->key_up), l = __ldcg(&h->key_low);
+            if (u < g_up) { g_up = u; w_up = r; }
+            if (l < g_low) { g_low = l; w_low = r; }
+        }
+        unpack_key_up(g_up, &b_hi, &i_hi);
+        unpack_key_low(g_low, &b_lo, &i_lo);
+        const CandHeader* h_hi = reinterpret_cast<const CandHeader*>(cand + (size_t)w_up * a.package);
+        const CandHeader* h_lo = reinterpret_cast<const CandHeader*>(cand + (size_t)w_low * a.package);
+        a_hi_old = __ldcg(&h_hi->a_hi); a_lo_old = __ldcg(&h_lo->a_lo);
+        m_y_hi = __ldcg(&h_hi->y_hi); m_y_lo = __ldcg(&h_lo->y_lo);
+        m_xsq_hi = __ldcg(&h_hi->xsq_hi); m_xsq_lo = __ldcg(&h_lo->xsq_lo);
+        m_src_hi = reinterpret_cast<const float4*>(h_hi + 1);                  // package: header, row_hi, row_lo
+        m_src_lo = reinterpret_cast<const float4*>(h_lo + 1) + a.pitch4;
+        return true;
+    };
+
+    if (a.world <= 1) {
+        // the selection left in the global keys by setup / the previous launch
         const unsigned long long k_up = a.keys[0], k_low = a.keys[1];
         unpack_key_up(k_up, &b_hi, &i_hi);
         unpack_key_low(k_low, &b_lo, &i_lo);
@@ -190,6 +240,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     // everyone has read alpha of the initial pair before any owner overwrites it
     if (!grid_barrier(a.barrier, bar_target, &s_flag)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
     bar_target += (unsigned int)G;
+    if (a.world > 1 && !acquire_remote((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
 
     uint64_t pol_keep, pol_stream;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
@@ -245,23 +296,32 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         if (a.trace && it == a.trace_iter && tid == 0) {
             unsigned long long t;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            a.trace[(size_t)cta * 4 + which] = t;
+            a.trace[(size_t)cta * 8 + which] = t;
         }
     };
 
     for (int it = 0;; ++it) {
         stamp(it, 0);
         // ================= pair -> rows, eta, alpha update (every CTA, identically) =================
-        const int r_hi = i_hi - a.index_base, r_lo = i_lo - a.index_base;
-        if (tid == 0) {
-            const uint32_t bytes = (uint32_t)a.pitch4 * 16u;
-            mbar_expect_tx(&s_bar, 2u * bytes);
-            tma_bulk_g2s(s_hi, a.x4 + (size_t)r_hi * a.pitch4, bytes, &s_bar);
-            tma_bulk_g2s(s_lo, a.x4 + (size_t)r_lo * a.pitch4, bytes, &s_bar);
+        const int r_hi = i_hi - a.index_base, r_lo = i_lo - a.index_base;     // may lie outside [0, n) on a multi-GPU run
+        int y_hi, y_lo;
+        float xsq_hi, xsq_lo;
+        if (a.world > 1) {
+            // rows travelled in the packages (written by peers over NVLink): plain L2 loads into smem
+            for (int i = tid; i < a.pitch4; i += kResThreads) { s_hi[i] = __ldcg(m_src_hi + i); s_lo[i] = __ldcg(m_src_lo + i); }
+            y_hi = m_y_hi; y_lo = m_y_lo; xsq_hi = m_xsq_hi; xsq_lo = m_xsq_lo;
+            __syncthreads();
+        } else {
+            if (tid == 0) {
+                const uint32_t bytes = (uint32_t)a.pitch4 * 16u;
+                mbar_expect_tx(&s_bar, 2u * bytes);
+                tma_bulk_g2s(s_hi, a.x4 + (size_t)r_hi * a.pitch4, bytes, &s_bar);
+                tma_bulk_g2s(s_lo, a.x4 + (size_t)r_lo * a.pitch4, bytes, &s_bar);
+            }
+            y_hi = __ldg(a.y + r_hi); y_lo = __ldg(a.y + r_lo);
+            xsq_hi = __ldg(a.xsq + r_hi); xsq_lo = __ldg(a.xsq + r_lo);
+            mbar_wait(&s_bar, (uint32_t)(it & 1));
         }
-        const int y_hi = __ldg(a.y + r_hi), y_lo = __ldg(a.y + r_lo);
-        const float xsq_hi = __ldg(a.xsq + r_hi), xsq_lo = __ldg(a.xsq + r_lo);
-        mbar_wait(&s_bar, (uint32_t)(it & 1));
         // |x_hi - x_lo|^2 exactly as the control kernel sums it: 256 strided partials, warp butterfly,
         // then the eight warp sums in order (svmTrain.cu:696-714 is the host original)
         if (tid < kCtlThreads) {
@@ -447,19 +507,30 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             }
             __syncthreads();
         }
+        // multi-GPU: CTA 0 publishes this rank's candidates to every rank (also on the last iteration of the
+        // launch: the next launch starts by waiting for exactly these packages)
+        stamp(it, 4);
+        if (a.world > 1 && cta == 0) push_package(*a.push, s_next_key[0], s_next_key[1], s_next[0], s_next[1], true, (unsigned int)num_iter);
+        stamp(it, 5);
         if (last_iter) {
             if (cta == 0 && tid == 0) {
                 a.keys[0] = s_next_key[0];
                 a.keys[1] = s_next_key[1];
+                if (a.world > 1) { a.push->keys_copy[0] = s_next_key[0]; a.push->keys_copy[1] = s_next_key[1]; }
                 if (!keep_going) { st->converged = 1; st->done = 1; }
                 if (num_iter >= a.max_iter) st->done = 1;
             }
             break;
         }
-        unpack_key_up(s_next_key[0], &b_hi, &i_hi);
-        unpack_key_low(s_next_key[1], &b_lo, &i_lo);
-        a_hi_old = s_next[0];
-        a_lo_old = s_next[1];
+        if (a.world > 1) {
+            if (!acquire_remote((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
+            stamp(it, 6);
+        } else {
+            unpack_key_up(s_next_key[0], &b_hi, &i_hi);
+            unpack_key_low(s_next_key[1], &b_lo, &i_lo);
+            a_hi_old = s_next[0];
+            a_lo_old = s_next[1];
+        }
         __syncthreads();        // s_next / s_cand are rewritten next round
     }
     if (cta == 0 && a.cache_lines > 0) {

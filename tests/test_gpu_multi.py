@@ -27,6 +27,8 @@ def _free_port():
 
 
 def _worker(rank, world, port, name, cache, exchange, out_dir):
+    graph_loop = exchange.endswith("+graph")
+    exchange = exchange.split("+")[0]
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
@@ -45,19 +47,21 @@ def _worker(rank, world, port, name, cache, exchange, out_dir):
     ids = [capi.comm_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(ids, src=0)
     with capi.Trainer(n, d, float(g["c"]), float(g["gamma"]), float(g["epsilon"]), max_iter=int(g["max_iter"]), cache_size=cache,
-                      shard_rows=cnt, shard_start=lo, device=rank, flags=capi.FLAG_X_SHARD_ONLY) as t:
+                      shard_rows=cnt, shard_start=lo, device=rank,
+                      flags=capi.FLAG_X_SHARD_ONLY | (capi.FLAG_GRAPH_LOOP if graph_loop else 0)) as t:
         t.comm_init(ids[0], rank, world)
         t.upload(np.ascontiguousarray(g["x"][lo:lo + cnt]), np.ascontiguousarray(g["y"][lo:lo + cnt]))
         st = t.train()
         alpha, f, _ = t.download()
         np.savez(os.path.join(out_dir, "r%d.npz" % rank), alpha=alpha, f=f, it=st.num_iter, conv=st.converged,
-                 b=st.b, hits=st.cache_hits, lo=lo, transport=t.comm_transport)
+                 b=st.b, hits=st.cache_hits, lo=lo, transport=t.comm_transport, resident=t.loop_info()[0])
     dist.barrier()
     dist.destroy_process_group()
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
 @pytest.mark.parametrize("name,cache,exchange", [("mnist_512", 0, "p2p"), ("adult_2048", 10, "p2p"), ("odd_d_333x37", 4, "p2p"),
+                                                 ("mnist_512", 10, "p2p+graph"), ("adult_2048", 0, "p2p+graph"),
                                                  ("mnist_512", 10, "nccl"), ("odd_d_333x37", 0, "nccl")])
 def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache, exchange):
     import torch.multiprocessing as mp
@@ -72,7 +76,8 @@ def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache, excha
         alpha, f, _ = t.download()
     parts = [np.load(tmp_path / ("r%d.npz" % r)) for r in range(world)]
     for p in parts:
-        assert str(p["transport"]) == exchange      # peer mapping must actually be in use when asked for
+        assert str(p["transport"]) == exchange.split("+")[0]      # peer mapping must actually be in use when asked for
+        assert bool(p["resident"]) == (exchange == "p2p")         # resident loop over peer memory, graph loop otherwise
         assert int(p["it"]) == st.num_iter and int(p["conv"]) == st.converged and float(p["b"]) == st.b
         assert int(p["hits"]) == st.cache_hits
     assert np.array_equal(np.concatenate([p["alpha"] for p in parts]), alpha)
