@@ -141,7 +141,8 @@ def run_reference(args):
     from oracle import pyoracle
     x, y, prm, n_total, d, _, _ = load_workload(args)
     kind = "reference" if pyoracle.have_ref() else "port"
-    ips = 2 if (args.steps + args.warmup) <= 40 else 1
+    total_steps = args.steps + args.warmup
+    ips = 4 if total_steps <= 40 else (2 if total_steps <= 100 else 1)      # keeps the whole run within a few minutes
 
     def step():
         if kind == "reference":

@@ -419,31 +419,31 @@ def test_predict_both_conventions(golden, oracle):
 
 
 def test_full_shape_properties(torch, oracle):
-    """BASELINE configs[1] shape (60000 x 784): properties that do not need the slow oracle --
-    selection exact on the device's own snapshot, f moves only by the pair's kernel columns,
-    sum(alpha*y) conserved while nothing is clipped, and agreement with the port over a short prefix."""
+    """BASELINE configs[1] at its FULL shape (60000 x 784), where seq.cpp itself would need hours:
+      * the first 48 pairs equal the oracle's in the same kernel form and tie rule (all host threads),
+        alpha and f within 1e-4 -- a prefix of the very run bench.py times;
+      * further on, properties that need no oracle run: the device's selection is exact on its own
+        snapshot, and sum(alpha * y) stays 0 while nothing has been clipped."""
     x, y, prm = datagen.make("mnist60k")
     n, d = x.shape
+    k = 48
+    r = oracle.train(x, y, prm["c"], prm["gamma"], prm["epsilon"], k, kernel_form=1, select_rule=1,
+                     nthreads=oracle.max_threads(), trace_cap=k)
     with capi.Trainer(n, d, prm["c"], prm["gamma"], prm["epsilon"], cache_size=10) as t:
         t.upload(x, y)
-        st = t.train(40)
-        assert st.num_iter == 40
+        for i in range(k):
+            st = t.train(1)
+            assert (st.i_hi, st.i_lo) == tuple(r.trace_idx[i]), "iteration %d" % i
+        alpha, f, _ = t.download()
+        assert np.abs(alpha - r.alpha).max() < 1e-4 and np.abs(f - r.f).max() < 1e-4
+        st = t.train(400)
+        assert st.num_iter == k + 400
         alpha, f, _ = t.download()
         rv, keys = t.step1()
         ih, il, bh, bl = oracle.select(alpha, y, f, prm["c"], rule=1)
         assert keys == (capi.pack_key_up(bh, ih), capi.pack_key_low(bl, il))
-        inner = (alpha > 0) & (alpha < prm["c"])
-        if inner.sum() == (alpha != 0).sum():
-            assert abs(float((alpha.astype(np.float64) * y).sum())) < 1e-4
-    r = oracle.train(x[:6000], y[:6000], prm["c"], prm["gamma"], prm["epsilon"], 25, kernel_form=1, select_rule=1,
-                     nthreads=oracle.max_threads(), trace_cap=25)
-    with capi.Trainer(6000, d, prm["c"], prm["gamma"], prm["epsilon"], cache_size=0) as t:
-        t.upload(np.ascontiguousarray(x[:6000]), np.ascontiguousarray(y[:6000]))
-        for k in range(25):
-            st = t.train(1)
-            assert (st.i_hi, st.i_lo) == tuple(r.trace_idx[k])
-        alpha, f, _ = t.download()
-    assert np.abs(alpha - r.alpha).max() < 1e-4 and np.abs(f - r.f).max() < 1e-4
+        if not (alpha == np.float32(prm["c"])).any():
+            assert abs(float((alpha.astype(np.float64) * y).sum())) < 1e-3
 
 
 # ------------------------------------------------------------------------------------------------
