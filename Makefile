@@ -46,7 +46,7 @@ $(LIB): $(CU_OBJS)
 host: $(HOST_LIB) $(CLI)
 
 $(HOST_LIB): $(HOST_SRCS) $(wildcard include/*.h include/*.hpp) $(LIB)
-	$(CXX) -O2 -std=c++17 -fPIC -Wall -shared -Iinclude -o $@ $(HOST_SRCS) -Ldpsvm_b200 -ldpsvm -Wl,-rpath,'$$ORIGIN'
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -pthread -shared -Iinclude -o $@ $(HOST_SRCS) -Ldpsvm_b200 -ldpsvm -Wl,-rpath,'$$ORIGIN'
 
 $(CLI): $(HOST)/svmTrainMain.cpp $(HOST_LIB)
 	$(CXX) -O2 -std=c++17 -Wall -Iinclude -o $@ $(HOST)/svmTrainMain.cpp -Ldpsvm_b200 -ldpsvm_host -ldpsvm -Wl,-rpath,'$$ORIGIN'

@@ -487,3 +487,22 @@ def test_loops_can_be_mixed_with_the_dropin_steps(golden):
         t.step2(t2.i_hi, t2.i_lo, float(a58[t2.i_hi]), float(a58[t2.i_lo]))      # a no-change directed step (delta = 0)
         a58b, f58b, _ = t.download()
         assert np.array_equal(a58b, a58) and np.allclose(f58b, f58, atol=0)
+
+
+def test_wide_rows_use_the_generic_kernels(oracle):
+    """d = 1100 (pitch4 > 256): runtime-length dot products, graph loop (the resident loop covers d <= 1024)."""
+    rng = np.random.default_rng(77)
+    n, d = 240, 1100
+    x = (rng.random((n, d), dtype=np.float32) < 0.1).astype(np.float32) * rng.random((n, d), dtype=np.float32)
+    y = np.where(rng.random(n) < 0.5, 1, -1).astype(np.int32)
+    ref = oracle.train(x, y, 10.0, 0.05, 1e-3, 150000, kernel_form=1, select_rule=1, nthreads=oracle.max_threads(), trace_cap=100)
+    with capi.Trainer(n, d, 10.0, 0.05, 1e-3, cache_size=10) as t:
+        assert t.loop_info()[0] is False
+        t.upload(x, y)
+        for k in range(40):
+            st = t.train(1)
+            assert (st.i_hi, st.i_lo) == tuple(ref.trace_idx[k])
+        st = t.train()
+        alpha, _, _ = t.download()
+    assert st.converged == 1 and abs(st.num_iter - ref.num_iter) <= max(1, round(0.01 * ref.num_iter))
+    assert abs(st.b - float(ref.b)) < 2e-3 and int((alpha != 0).sum()) == int((ref.alpha != 0).sum())
