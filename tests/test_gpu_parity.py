@@ -506,3 +506,38 @@ def test_wide_rows_use_the_generic_kernels(oracle):
         alpha, _, _ = t.download()
     assert st.converged == 1 and abs(st.num_iter - ref.num_iter) <= max(1, round(0.01 * ref.num_iter))
     assert abs(st.b - float(ref.b)) < 2e-3 and int((alpha != 0).sum()) == int((ref.alpha != 0).sum())
+
+
+@pytest.mark.parametrize("workload,sample", [("adult32k", 384), ("mnist60k", 192)])
+def test_converged_state_is_consistent_at_full_shape(workload, sample):
+    """BASELINE configs[1] and [2] at full size, trained to convergence (30-46 thousand in-place f updates):
+      * f recomputed from scratch in float64, f_i = sum_j alpha_j y_j K(x_j, x_i) - y_i, agrees with the
+        device's incrementally updated f on a row sample (no drift, no lost update);
+      * the stopping rule holds on the downloaded state: max f over I_low <= min f over I_up + 2 eps;
+      * sum_i alpha_i y_i stays small relative to sum_i alpha_i.  It is NOT exactly conserved by the
+        reference's update: alpha_hi is formed from the UNCLIPPED alpha_lo and both are then clipped
+        (seq.cpp:238-243), so every clip at 0 or C leaks -- seq.cpp's own golden solutions show
+        |sum alpha y| up to 0.33 against sum alpha = 379 (mnist_4096)."""
+    x, y, prm = datagen.make(workload)
+    n, d = x.shape
+    c, gamma, eps = prm["c"], prm["gamma"], prm["epsilon"]
+    with capi.Trainer(n, d, c, gamma, eps, max_iter=2000000, cache_size=10) as t:
+        t.upload(x, y)
+        st = t.train()
+        alpha, f, _ = t.download()
+    assert st.converged == 1 and np.isfinite(alpha).all() and (alpha >= 0).all() and (alpha <= np.float32(c)).all()
+    rng = np.random.default_rng(5)
+    rows = rng.choice(n, sample, replace=False)
+    sv = np.flatnonzero(alpha != 0)
+    xs = x[sv].astype(np.float64)
+    coef = alpha[sv].astype(np.float64) * y[sv]
+    xsq = (xs ** 2).sum(1)
+    for i in rows:
+        xi = x[i].astype(np.float64)
+        k = np.exp(-gamma * (xsq + (xi ** 2).sum() - 2.0 * (xs @ xi)))
+        assert abs(float(coef @ k) - y[i] - float(f[i])) < 2e-3, i
+    up = np.where(alpha == 0, y == 1, np.where(alpha == np.float32(c), y == -1, True))
+    low = np.where(alpha == 0, y != 1, np.where(alpha == np.float32(c), y != -1, True))
+    # the last iteration still applied its update, so the state is at most one step past the test
+    assert f[low].max() <= f[up].min() + 2 * eps + 5e-3
+    assert abs(float((alpha.astype(np.float64) * y).sum())) < 1e-2 * float(alpha.sum())
