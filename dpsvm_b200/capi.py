@@ -80,9 +80,10 @@ def lib():
     """Load libdpsvm.so (once).  Raises if it is missing: the product has no other path."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise FileNotFoundError(LIB_PATH + " not built -- run __graft_entry__.build() or `make lib`")
-        L = C.CDLL(LIB_PATH)
+        path = os.environ.get("DPSVM_LIB", LIB_PATH)          # A/B timing of two builds; normally the in-tree library
+        if not os.path.exists(path):
+            raise FileNotFoundError(path + " not built -- run __graft_entry__.build() or `make lib`")
+        L = C.CDLL(path)
         L.dpsvm_last_error.restype = C.c_char_p
         L.dpsvm_pack_key_up.restype = C.c_uint64
         L.dpsvm_pack_key_up.argtypes = [C.c_float, C.c_int32]

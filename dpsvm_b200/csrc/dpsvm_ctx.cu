@@ -486,9 +486,13 @@ int dpsvm_upload(dpsvm_ctx* c, const float* h_x, const int32_t* h_y)
     if (!c || !h_x || !h_y) return fail(DPSVM_ERR_INVALID, "dpsvm_upload: null argument");
     CU(cudaSetDevice(c->device));
     const int d = c->p.num_attributes;
-    if (c->pitch != d) CU(cudaMemsetAsync(c->d_x, 0, sizeof(float) * (size_t)c->res_n * c->pitch, c->stream));
-    CU(cudaMemcpy2DAsync(c->d_x, sizeof(float) * (size_t)c->pitch, h_x, sizeof(float) * (size_t)d, sizeof(float) * (size_t)d,
-                         (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+    if (c->pitch != d) {
+        CU(cudaMemsetAsync(c->d_x, 0, sizeof(float) * (size_t)c->res_n * c->pitch, c->stream));
+        CU(cudaMemcpy2DAsync(c->d_x, sizeof(float) * (size_t)c->pitch, h_x, sizeof(float) * (size_t)d, sizeof(float) * (size_t)d,
+                             (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+    } else {
+        CU(cudaMemcpyAsync(c->d_x, h_x, sizeof(float) * (size_t)c->res_n * d, cudaMemcpyHostToDevice, c->stream));
+    }
     CU(cudaMemcpyAsync(c->d_y, h_y, sizeof(int) * (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
     return finish_upload(c);
 }

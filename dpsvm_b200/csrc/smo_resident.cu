@@ -41,12 +41,14 @@ __device__ __forceinline__ bool grid_barrier(unsigned int* counter, unsigned int
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
-        atomicAdd(counter, 1u);
+        // the last CTA to arrive is the critical path: it learns from its own atomic that everyone is
+        // here and skips the polling round trip
+        const unsigned int before = atomicAdd(counter, 1u);
         int ok = 1;
         unsigned long long t0;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
         unsigned int spins = 0;
-        while (ld_acquire_gpu_u32(counter) < target) {
+        while (before + 1u < target && ld_acquire_gpu_u32(counter) < target) {
             if ((++spins & 0x3FFu) == 0) {
                 unsigned long long t1;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
