@@ -1,6 +1,7 @@
 // smo_resident.cu -- the "resident loop": up to `chunk` complete SMO iterations inside ONE persistent,
 // cooperatively launched kernel (one CTA per SM), replacing the [control kernel, pass kernel] pair
-// of the graph loop for the common case (single GPU, small or no kernel-row cache).
+// of the graph loop for the common case (rows up to 1 024 floats, kernel-row cache of at most 64 lines;
+// one GPU, or several over the peer-memory exchange).
 //
 // Same arithmetic as the graph loop, bit for bit (same dot-product order, same eta reduction order,
 // same epilogue), so the two loops are interchangeable and are tested against each other.
@@ -9,17 +10,24 @@
 // 190-302) and the cache lookups (cache.cu:62-105).
 //
 // Why it is faster than two kernels per iteration:
-//   * X-stationary slice: each CTA keeps the first rows of its row range in shared memory for the
-//     whole launch (about 68 rows of 784 floats per SM, 17 % of a 60 000-row X) -- those rows are
-//     never re-read from HBM/L2; only the rest of the range streams every iteration.
 //   * No leader, no kernel boundary: after its sweep a CTA publishes its block-best candidates (keys
 //     plus the alpha of those rows) in a per-CTA slot and arrives at a grid barrier; every CTA then
 //     reads all slots and derives the next pair, eta and the alpha update REDUNDANTLY and
 //     identically.  The dependency chain per iteration is barrier -> slots -> two rows by TMA ->
-//     block reduction, instead of two kernel boundaries around a single-CTA control kernel.
+//     block reduction (2.8 us), instead of two kernel boundaries around a single-CTA control kernel
+//     (5.6 us).
+//   * On-chip slice: each CTA keeps some units of its row range -- rows AND their |x|^2, y, f, alpha --
+//     in shared memory for the whole launch; they are never re-read from HBM/L2.  The whole shard when it
+//     fits (Adult 32 561 x 123, or a 7 500-row shard of an 8-GPU run), otherwise 16 units per CTA: the
+//     carve-out comes out of L1, and L1 capacity bounds the streaming loads an SM keeps in flight
+//     (profiles/r01_resident_trace.md).
+//   * The first streamed unit of the next iteration is loaded into registers before the barrier, so HBM
+//     keeps streaming through the dependency chain.
 //   * The kernel-row cache's LRU bookkeeping is a replicated state machine: every CTA holds the same
 //     small table in shared memory and applies the same lookups, so no CTA waits for another's
 //     decision.
+//   * Multi-GPU: after the local barrier CTA 0 stores the rank's candidate package into every peer's
+//     mailbox over NVLink; every CTA then waits on the arrival flags and merges the packages itself.
 #include <limits.h>
 #include <math.h>
 #include <stdlib.h>
