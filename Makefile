@@ -8,7 +8,7 @@ NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unknow
 CSRC      := dpsvm_b200/csrc
 OBJDIR    := build
 LIB       := dpsvm_b200/libdpsvm.so
-CU_SRCS   := $(CSRC)/smo_kernels.cu $(CSRC)/dpsvm_ctx.cu $(CSRC)/predict.cu $(CSRC)/comm.cu $(CSRC)/host_utils.cu $(CSRC)/noalloc.cu $(CSRC)/smo_resident.cu
+CU_SRCS   := $(CSRC)/smo_kernels.cu $(CSRC)/dpsvm_ctx.cu $(CSRC)/predict.cu $(CSRC)/comm.cu $(CSRC)/host_utils.cu $(CSRC)/noalloc.cu $(CSRC)/smo_resident.cu $(CSRC)/smo_sparse.cu
 CU_OBJS   := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS))
 HDRS      := $(wildcard $(CSRC)/*.cuh) include/dpsvm_cuda.h
 

@@ -127,10 +127,12 @@ def load_workload(args, rank=0, world=1, shard_only=False):
     return x, y, prm, n_total, d, n_total, 0
 
 
-def algorithmic_bytes(n, d, cache_lines):
+def algorithmic_bytes(n, d, cache_lines, nnz=None):
     """X shard once + |x|^2, f read, f write, alpha, y at 4 B each (logical d); the two
-    cache-line stores of a miss/miss iteration add 8 n when the kernel-row cache is on."""
-    return 4.0 * n * d + 20.0 * n + (8.0 * n if cache_lines >= 2 else 0.0)
+    cache-line stores of a miss/miss iteration add 8 n when the kernel-row cache is on.
+    nnz given (sparse stream): X costs 6 B per non-zero (fp32 value + 16-bit column), padding excluded."""
+    x_bytes = 4.0 * n * d if nnz is None else 6.0 * nnz
+    return x_bytes + 20.0 * n + (8.0 * n if cache_lines >= 2 else 0.0)
 
 
 def run_reference(args):
@@ -258,7 +260,8 @@ def main():
 
     # ---- the dominant kernel alone (stateless launcher, back to back on one stream) -----------
     pass_ms = None
-    if not args.no_pass_only:
+    lanes, nnz, sweep_bytes = tr.layout_info()
+    if not args.no_pass_only and lanes == 0:        # the stateless pass entry point sweeps dense rows
         s = tr.device_state()
         pitch = s["pitch"]
         keys = torch.full((2,), -1, dtype=torch.int64, device="cuda")
@@ -328,12 +331,14 @@ def main():
         return
 
     peak, peak_src = measured_peak()
-    abytes = algorithmic_bytes(n_shard, d, args.cache_size)
+    abytes = algorithmic_bytes(n_shard, d, args.cache_size, nnz if lanes else None)
+    dense_abytes = algorithmic_bytes(n_shard, d, args.cache_size)
     iter_ms = ms / max(done_iters, 1)
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
-            per_iter = json.load(fh).get(("%s_per_iteration" % args.workload) if world == 1 else "%s_p%d_per_iteration" % (args.workload, world))
+            key = "%s%s_per_iteration" % (args.workload, "_sparse" if lanes else "")
+            per_iter = json.load(fh).get(key if world == 1 else "%s%s_p%d_per_iteration" % (args.workload, "_sparse" if lanes else "", world))
             traffic = per_iter
     except Exception:
         pass
@@ -350,7 +355,7 @@ def main():
         gpu_launches = launches
     else:
         kernels_per_iter = 3 if tr.comm_transport == "nccl" else 2     # control + pass (+ pack before the NCCL all-gather)
-        kernel_name = "smo_pass_kernel"
+        kernel_name = "smo_pass_sparse_kernel" if lanes else "smo_pass_kernel"
         kernel_ms = pass_ms if pass_ms is not None else iter_ms
         bytes_per_launch = abytes
         timing = ("pass kernel alone: 200 launches replayed from one CUDA graph with the trainer's L2 policy and sweep order, "
@@ -372,12 +377,19 @@ def main():
             "loop": "resident (persistent cooperative kernel, %d iterations per launch)" % chunk if resident
                     else "CUDA graph of [control, pass] x %d" % chunk,
             "pass_kernel_alone_us": (1e3 * pass_ms) if pass_ms is not None else None,
-            "l2": "X shard %.1f MB per pass vs 126 MB L2: %s" % (4e-6 * n_shard * d, "inputs larger than L2" if 4.0 * n_shard * d > 126e6 else "L2-resident"),
+            "layout": ("sparse stream, %d lanes per row: %.1f %% of the cells are non-zero, %.1f MB per sweep (padding included) instead of %.1f MB of dense rows"
+                       % (lanes, 100.0 * nnz / (n_shard * d), 1e-6 * sweep_bytes, 4e-6 * n_shard * d)) if lanes
+                      else "dense rows, %.1f MB per sweep" % (1e-6 * sweep_bytes),
+            "l2": "%.1f MB per sweep vs 126 MB L2: %s; consecutive iterations sweep in opposite directions, nothing is flushed between them (the loop re-reads the same X by construction)"
+                  % (1e-6 * sweep_bytes, "inputs larger than L2" if sweep_bytes > 126e6 else "L2-resident"),
             "iteration_GBps_incl_control": abytes / (iter_ms * 1e-3) / 1e9,
         },
         "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_iteration": abytes,
+                     "algorithmic_bytes_basis": ("sparse stream: 6 B per non-zero + 20 B per row (+ 8 B per row of cache-line stores)" if lanes
+                                                 else "SURVEY 8(d): 4 n d + 20 n (+ 8 n of cache-line stores)"),
+                     "dense_rows_equivalent_GBps": dense_abytes / (iter_ms * 1e-3) / 1e9,
                      "kernel_us": 1e3 * kernel_ms, "timing": timing, "share_of_step": share},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(4 * n_shard * d + 4 * n_shard),
                 "d2h_bytes_per_step": int(4 * n_shard + 64), "iters_per_step": e2e_iters,

@@ -18,6 +18,8 @@ OK = 0
 FLAG_NO_GRAPH = 1
 FLAG_X_SHARD_ONLY = 2
 FLAG_GRAPH_LOOP = 4
+FLAG_DENSE = 8
+FLAG_SPARSE = 16
 KEY_EMPTY = 0xFFFFFFFFFFFFFFFF
 COMM_ID_BYTES = 128
 
@@ -69,7 +71,7 @@ EXPORTS = [
     "dpsvm_pitch_for", "dpsvm_pass_variant", "dpsvm_pack_key_up", "dpsvm_pack_key_low", "dpsvm_unpack_key_up", "dpsvm_unpack_key_low",
     "dpsvm_row_norms", "dpsvm_init_state", "dpsvm_select", "dpsvm_smo_pass", "dpsvm_create", "dpsvm_destroy",
     "dpsvm_upload", "dpsvm_upload_device", "dpsvm_reset", "dpsvm_step1", "dpsvm_step2", "dpsvm_train",
-    "dpsvm_train_async", "dpsvm_loop_info", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
+    "dpsvm_train_async", "dpsvm_loop_info", "dpsvm_layout_info", "dpsvm_sync", "dpsvm_stream", "dpsvm_download", "dpsvm_device_state", "dpsvm_cache_lookup",
     "dpsvm_predict", "dpsvm_comm_unique_id", "dpsvm_comm_init", "dpsvm_comm_transport", "dpsvm_smo_iteration_noalloc",
 ]
 
@@ -103,6 +105,7 @@ def lib():
         L.dpsvm_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.dpsvm_upload_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.dpsvm_reset.argtypes = [C.c_void_p]
+        L.dpsvm_layout_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
         L.dpsvm_step1.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
         L.dpsvm_step2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.dpsvm_train.argtypes = [C.c_void_p, C.c_int, C.POINTER(TrainStatus)]
@@ -300,6 +303,12 @@ class Trainer:
         r, k = C.c_int(), C.c_int()
         check(lib().dpsvm_loop_info(self._h, C.byref(r), C.byref(k)))
         return bool(r.value), k.value
+
+    def layout_info(self):
+        """(lanes, nnz, sweep_bytes) -- lanes 0 = dense rows, else the sparse stream; see dpsvm_layout_info."""
+        g, nnz, b = C.c_int(), C.c_longlong(), C.c_longlong()
+        check(lib().dpsvm_layout_info(self._h, C.byref(g), C.byref(nnz), C.byref(b)))
+        return g.value, nnz.value, b.value
 
     @property
     def stream(self):

@@ -48,6 +48,7 @@ static void free_all(dpsvm_ctx* c)
     cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
     cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
     cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru);
+    sparse_release(c);
     predict_free(c);
     comm_free(c);
     if (c->h_st) cudaFreeHost(c->h_st);
@@ -81,6 +82,7 @@ PassDev make_pass_args(dpsvm_ctx* c)
     a.early_load = c->cache.lines < 64;
     a.pdl = c->pdl;
     a.push = c->d_push;
+    a.sp = c->sp;
     return a;
 }
 
@@ -198,6 +200,7 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.lru_key = c->d_lru;
     a.lru_stamp = c->d_lru + kResCacheLines;
     a.lru_meta = c->d_lru + 2 * kResCacheLines;
+    a.sp = c->sp;
     a.world = 1;
     if (c->world > 1 && !comm_fill_resident(c, &a)) return fail(DPSVM_ERR_STATE, "resident loop needs the peer-memory exchange");
     static unsigned long long* d_trace = nullptr;
@@ -476,7 +479,16 @@ int dpsvm_destroy(dpsvm_ctx* c)
 
 static int finish_upload(dpsvm_ctx* c)
 {
-    CU(launch_row_norms(c->d_x, c->res_n, c->pitch, c->d_xsq, c->stream));
+    // a captured graph holds the previous upload's sparse-stream pointers: rebuild it lazily
+    if (c->gexec) { cudaGraphExecDestroy(c->gexec); c->gexec = nullptr; }
+    if (c->graph) { cudaGraphDestroy(c->graph); c->graph = nullptr; }
+    int rc = sparse_setup(c);       // layout decision, sparse stream, |x|^2 in the matching order
+    if (rc != DPSVM_OK) return rc;
+    if (!getenv("DPSVM_VARIANT")) {
+        // L2 policy follows what the sweep actually reads: hints and a pinned prefix once that outgrows L2
+        const double mb = c->sp.val ? 192e-6 * (double)c->sp.total_steps : 4e-6 * (double)c->p.shard_rows * (double)c->pitch;
+        c->variant = mb > 64.0 ? (2 | (32 << 8)) : 0;
+    }
     c->uploaded = true;
     return reset_state(c);
 }
@@ -611,6 +623,16 @@ int dpsvm_loop_info(dpsvm_ctx* c, int* resident, int* chunk)
     if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_loop_info: null context");
     if (resident) *resident = (c->loop_resident && (c->world == 1 || c->exchange_p2p)) ? 1 : 0;
     if (chunk) *chunk = c->chunk;
+    return DPSVM_OK;
+}
+
+int dpsvm_layout_info(dpsvm_ctx* c, int* lanes, long long* nnz, long long* sweep_bytes)
+{
+    if (!c) return fail(DPSVM_ERR_INVALID, "dpsvm_layout_info: null context");
+    if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_layout_info before dpsvm_upload");
+    if (lanes) *lanes = c->sp.val ? c->sp.lanes : 0;
+    if (nnz) *nnz = c->sp_nnz;
+    if (sweep_bytes) *sweep_bytes = c->sp.val ? 192ll * (long long)c->sp.total_steps : 4ll * c->p.shard_rows * (long long)c->pitch;
     return DPSVM_OK;
 }
 

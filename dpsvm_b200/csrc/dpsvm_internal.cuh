@@ -36,6 +36,14 @@ struct dpsvm_ctx {
 
     dpsvm::CacheDev cache{};
 
+    // sparse stream of the owned rows (smo_sparse.cu); sp.val == null: the sweep reads the dense rows
+    dpsvm::SparseDev sp{};
+    float* d_sp_val = nullptr;
+    unsigned int* d_sp_col2 = nullptr;
+    unsigned int* d_sp_unit_off = nullptr;
+    int* d_sp_cta_first = nullptr;
+    long long sp_nnz = -1;       // non-zeros of the owned rows (-1: not counted, dense layout forced)
+
     // resident loop (smo_resident.cu)
     int loop_resident = 0;       // 1: the persistent cooperative kernel runs the iterations
     dpsvm::ResSlot* d_slots = nullptr;
@@ -65,6 +73,9 @@ CtlDev make_ctl_args(dpsvm_ctx* c);
 
 // cache_host.cu
 int cache_lookup_host(dpsvm_ctx* c, int key, int* line, int* hit);
+// smo_sparse.cu: layout decision, sparse stream, row norms in the matching order (called by every upload)
+int sparse_setup(dpsvm_ctx* c);
+void sparse_release(dpsvm_ctx* c);
 // predict.cu
 void predict_free(dpsvm_ctx* c);
 // comm.cu

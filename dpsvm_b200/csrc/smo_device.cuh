@@ -72,6 +72,69 @@ __device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
 }
 
 // ------------------------------------------------------------------------------------------------
+// Sparse sweep building blocks (layout and order: SparseDev in smo_kernels.cuh).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float ldg_f32_pol(const float* p, uint64_t pol)
+{
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ unsigned int ldg_u32_pol(const unsigned int* p, uint64_t pol)
+{
+    unsigned int v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    return v;
+}
+
+struct SpChunk {
+    float v[kSpChunk];
+    unsigned int c2[kSpChunk / 2];
+};
+
+// Steps [step0, step0 + min(steps_left, kSpChunk)) of a unit for this lane; step0 is even.  What lies past
+// the unit's end is value 0 / offset 0: an FMA with it leaves the accumulators as they are.
+__device__ __forceinline__ void sp_load_chunk(SpChunk& ch, const SparseDev& sp, unsigned int step0, int steps_left,
+                                              int lane, uint64_t pol)
+{
+    const float* vp = sp.val + (size_t)step0 * 32 + lane;
+    const unsigned int* cp = sp.col2 + (size_t)(step0 >> 1) * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < kSpChunk; j += 2) {
+        const bool ok = j < steps_left;             // steps come in pairs (kSpStepAlign == 2)
+        ch.v[j] = ok ? ldg_f32_pol(vp + j * 32, pol) : 0.f;
+        ch.v[j + 1] = ok ? ldg_f32_pol(vp + (j + 1) * 32, pol) : 0.f;
+        ch.c2[j / 2] = ok ? ldg_u32_pol(cp + (j / 2) * 32, pol) : 0u;
+    }
+}
+
+// s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]); c2 holds BYTE offsets into it.
+__device__ __forceinline__ void sp_fma_chunk(const SpChunk& ch, const float2* s_hl, float& acc_hi, float& acc_lo)
+{
+    const unsigned char* base = reinterpret_cast<const unsigned char*>(s_hl);
+#pragma unroll
+    for (int j = 0; j < kSpChunk; j += 2) {
+        const unsigned int w = ch.c2[j / 2];
+        const float2 h0 = *reinterpret_cast<const float2*>(base + (w & 0xFFFFu));
+        const float2 h1 = *reinterpret_cast<const float2*>(base + (w >> 16));
+        acc_hi = __fmaf_rn(ch.v[j], h0.x, acc_hi);
+        acc_lo = __fmaf_rn(ch.v[j], h0.y, acc_lo);
+        acc_hi = __fmaf_rn(ch.v[j + 1], h1.x, acc_hi);
+        acc_lo = __fmaf_rn(ch.v[j + 1], h1.y, acc_lo);
+    }
+}
+
+template <int G>
+__device__ __forceinline__ void sp_group_sum(float& acc_hi, float& acc_lo)
+{
+#pragma unroll
+    for (int off = G / 2; off >= 1; off >>= 1) {
+        acc_hi = __fadd_rn(acc_hi, __shfl_xor_sync(0xffffffffu, acc_hi, off));
+        acc_lo = __fadd_rn(acc_lo, __shfl_xor_sync(0xffffffffu, acc_lo, off));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Peer-memory candidate exchange (multi-GPU).  Runs in ONE block: builds this rank's package from
 // its local selection and stores it into slot (seq & 1) of every rank's mailbox -- stores to
 // CUDA-IPC-mapped peer memory travel over NVLink -- then raises this rank's flag there to seq + 1.

@@ -344,6 +344,110 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
 }
 
 // ------------------------------------------------------------------------------------------------
+// Fused pass over the sparse stream (layout and order: SparseDev, smo_kernels.cuh).  G lanes per row,
+// 32/G rows per warp at a time; a warp walks the steps of its unit in register chunks, one chunk ahead
+// in flight; the selected pair sits in shared memory interleaved as (x_hi[c], x_lo[c]) so that one
+// 64-bit shared load serves both dot products of a non-zero.
+// ------------------------------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const PassDev a)
+{
+    constexpr int GROUPS = 32 / G;
+    __shared__ __align__(16) float2 s_hl[kSparseMaxPitch];
+    __shared__ unsigned long long s_red[2 * (kPassThreads / 32)];
+    __shared__ int s_pushflag;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int sub = lane % G, grp = lane / G;
+    const int n_units = a.sp.n_units;
+    const int unit_stride = gridDim.x * (kPassThreads / 32);
+
+    uint64_t pol_keep, pol_stream;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+    if (a.sp.pin_steps) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+    else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol_stream));
+
+    int unit = blockIdx.x * (kPassThreads / 32) + warp;
+    SpChunk nxt;
+    unsigned int ubeg = 0;
+    int T = 0;
+    auto open_unit = [&](int k, unsigned int& beg, int& steps) {
+        const int u = a.reverse ? (n_units - 1 - k) : k;
+        beg = __ldg(a.sp.unit_off + u);
+        steps = (int)(__ldg(a.sp.unit_off + u + 1) - beg);
+    };
+    auto policy = [&](unsigned int beg) { return beg < a.sp.pin_steps ? pol_keep : pol_stream; };
+
+    // the stream does not depend on the pair: first chunk in flight before the dependency wait
+    bool loaded = false;
+    if (a.early_load && unit < n_units) {
+        open_unit(unit, ubeg, T);
+        sp_load_chunk(nxt, a.sp, ubeg, T, lane, policy(ubeg));
+        loaded = true;
+    }
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    const PassScalars sc = a.dev ? *a.dev : a.imm;
+    if (!sc.active) return;
+    unsigned long long best_up = DPSVM_KEY_EMPTY, best_low = DPSVM_KEY_EMPTY;
+    if (sc.both_hit) {
+        pass_both_hit(sc, a, best_up, best_low);
+        publish_keys(best_up, best_low, a.keys, s_red);
+        push_if_last(a.push, &s_pushflag);
+        return;
+    }
+    for (int i = tid; i < a.pitch4; i += kPassThreads) {
+        const float4 h = __ldcg(a.x_hi4 + i), l = __ldcg(a.x_lo4 + i);
+        s_hl[4 * i + 0] = make_float2(h.x, l.x);
+        s_hl[4 * i + 1] = make_float2(h.y, l.y);
+        s_hl[4 * i + 2] = make_float2(h.z, l.z);
+        s_hl[4 * i + 3] = make_float2(h.w, l.w);
+    }
+    __syncthreads();
+
+    if (unit < n_units && !loaded) {
+        open_unit(unit, ubeg, T);
+        sp_load_chunk(nxt, a.sp, ubeg, T, lane, policy(ubeg));
+    }
+    int t0 = 0;
+    float acc_hi = 0.f, acc_lo = 0.f;
+    float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
+    int e_y = 0, erow = 0;
+    bool eown = false;
+    while (unit < n_units) {
+        const SpChunk cur = nxt;
+        int unit_n = unit, t0_n = t0 + kSpChunk;
+        unsigned int ubeg_n = ubeg;
+        int T_n = T;
+        if (t0_n >= T) {
+            unit_n = unit + unit_stride;
+            t0_n = 0;
+            if (unit_n < n_units) open_unit(unit_n, ubeg_n, T_n);
+        }
+        if (unit_n < n_units) sp_load_chunk(nxt, a.sp, ubeg_n + (unsigned int)t0_n, T_n - t0_n, lane, policy(ubeg_n));
+        if (t0 == 0) {
+            const int u = a.reverse ? (n_units - 1 - unit) : unit;
+            erow = u * GROUPS + grp;
+            eown = (sub == 0) && (erow < a.n);
+            if (eown) {
+                e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow);
+                e_f = a.f[erow]; e_alpha = a.alpha[erow];
+            }
+        }
+        sp_fma_chunk(cur, s_hl, acc_hi, acc_lo);
+        if (t0_n == 0) {
+            sp_group_sum<G>(acc_hi, acc_lo);
+            if (eown) row_epilogue(erow, acc_hi, acc_lo, e_xsq, e_f, e_alpha, e_y, sc, a, true, best_up, best_low);
+            acc_hi = 0.f; acc_lo = 0.f;
+        }
+        unit = unit_n; t0 = t0_n; ubeg = ubeg_n; T = T_n;
+    }
+    publish_keys(best_up, best_low, a.keys, s_red);
+    push_if_last(a.push, &s_pushflag);
+}
+
+// ------------------------------------------------------------------------------------------------
 // |x_i|^2 with the pass's accumulation order.
 // ------------------------------------------------------------------------------------------------
 template <int LPR, int ITERS>
@@ -785,9 +889,30 @@ static cudaError_t launch_pass_lpr(int iters, const PassDev& a, int variant, cud
     return cudaErrorInvalidValue;
 }
 
+cudaError_t launch_pass_sparse(const PassDev& a0, int variant, cudaStream_t s)
+{
+    PassDev a = a0;
+    if (a.pitch4 * 4 > kSparseMaxPitch) return cudaErrorInvalidValue;
+    int blocks = (a.sp.n_units + (kPassThreads / 32) - 1) / (kPassThreads / 32);
+    const int cap = device_sm_count() * 2;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    a.reverse = variant & 1;
+    // same L2 budget as the dense pass: a prefix of the stream is loaded evict_last once it outgrows L2
+    a.sp.pin_steps = (variant & 2) ? (unsigned int)((double)((variant >> 8) & 0xFFFFF) * 1e6 / 192.0) : 0u;
+    switch (a.sp.lanes) {
+        case 4: return launch_ex(smo_pass_sparse_kernel<4>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 8: return launch_ex(smo_pass_sparse_kernel<8>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 16: return launch_ex(smo_pass_sparse_kernel<16>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 32: return launch_ex(smo_pass_sparse_kernel<32>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+    }
+    return cudaErrorInvalidValue;
+}
+
 cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s)
 {
     if (a.n <= 0) return cudaSuccess;
+    if (a.sp.val) return launch_pass_sparse(a, variant, s);
     if (a.pitch4 > 256) {
         const int cap4 = ((a.pitch4 + 31) / 32) * 32;
         const size_t smem = (size_t)cap4 * 2 * sizeof(float4);

@@ -12,6 +12,40 @@ constexpr int kCacheSmemLines = 3584;   // caches up to this many lines keep the
 
 struct PushDev;
 
+// ------------------------------------------------------------------------------------------------
+// Sparse stream of the owned rows (smo_sparse.cu).  X itself stays in HBM as dense rows -- the selected
+// pair, the candidate packages and predict read those -- but the per-iteration sweep, which is what
+// the loop is bound by, reads this compressed copy instead when the data is sparse enough (MNIST is
+// 19 % non-zero, Adult 11 %): value (4 B) + column (2 B) per non-zero instead of 4 B per cell.
+//
+// Layout ("sliced ELL", slices of 32/G rows, G lanes per row):  a UNIT is 32/G consecutive rows; row
+// r of the unit belongs to lane group r.  The non-zeros of a row, in ascending column order, are dealt
+// round-robin to the G lanes of its group: entry e goes to lane e % G, step e / G.  A unit has
+// T = unit_off[u+1] - unit_off[u] steps (the longest row of the unit, rounded up to kSpStepAlign;
+// shorter rows are padded with value 0 / column 0, which leave an FMA accumulator unchanged).  Step t
+// of the unit is 32 values  val[(unit_off[u] + t) * 32 + lane]  -- one coalesced 128 B load per warp --
+// and the byte offsets (8 * column, into the interleaved (x_hi, x_lo) float2 row in shared memory)
+// of two consecutive steps share one 32-bit word:  col2[((unit_off[u] + t) / 2) * 32 + lane].
+//
+// Dot-product order of the sparse layout (the counterpart of DotGeom): per lane sequential FMAs over
+// its entries in step order, then an xor-butterfly over the G lanes.  The row norms of a sparse
+// context are summed in the same order (sparse_row_norms), so <x_i,x_i> == |x_i|^2 stays bit-exact.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSpStepAlign = 2;
+constexpr int kSpChunk = 16;            // steps per register chunk (one chunk ahead is in flight)
+struct SparseDev {
+    const float* val;           // null: dense sweep
+    const unsigned int* col2;
+    const unsigned int* unit_off;   // [n_units + 1] first step of each unit
+    const int* cta_first;       // [grid + 1] first unit of each CTA of the resident loop (balanced by steps)
+    int lanes;                  // G: 4, 8, 16 or 32
+    int n_units;
+    int grid;                   // CTAs cta_first was computed for
+    int max_cta_units;          // largest cta_first[i+1] - cta_first[i]
+    unsigned int total_steps;
+    unsigned int pin_steps;     // filled by the launcher: steps per CTA loaded L2::evict_last
+};
+
 // Arguments of the fused pass kernel (by value; small enough for the parameter space).
 struct PassDev {
     const float4* x4;       // [n x pitch4] owned rows
@@ -32,6 +66,7 @@ struct PassDev {
     PassScalars imm;            // used when dev == nullptr
     const PassScalars* dev;     // device-resident scalars written by the control kernel
     const PushDev* push;        // multi-GPU peer-memory exchange: last CTA publishes the candidates (else null)
+    SparseDev sp;               // sp.val != null: sweep the sparse stream instead of x4
 };
 
 // Kernel-row cache (device-resident LRU).  line_of_key is a direct index over the GLOBAL row
@@ -168,9 +203,12 @@ struct ResidentDev {
     size_t package;
     unsigned long long* trace;  // optional [grid][4] globaltimer stamps of iteration trace_iter (DPSVM_TRACE)
     int trace_iter;
+    SparseDev sp;               // sp.val != null: sweep the sparse stream instead of x4
 };
 
 bool resident_supported(int pitch4, int cache_lines);
+int resident_grid();            // CTAs of the resident loop on the current device (one per SM)
+cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream_t s);
 cudaError_t launch_resident(const ResidentDev& a, int variant, cudaStream_t s);
 
 int device_sm_count();
@@ -183,5 +221,15 @@ cudaError_t launch_control(const CtlDev& a, cudaStream_t s);
 cudaError_t launch_pack(const PackDev& a, cudaStream_t s);
 cudaError_t launch_push(const PushDev* d_push, cudaStream_t s);   // publish the current local selection (initial package)
 cudaError_t launch_cache_lookup(const CacheDev& c, int key, int* d_out, cudaStream_t s);
+cudaError_t launch_pass_sparse(const PassDev& a, int variant, cudaStream_t s);
+
+// smo_sparse.cu -- building the sparse stream from the dense rows (setup time)
+constexpr int kSparseMaxPitch = 1024;   // floats per row the sparse sweep supports (one 8 KB float2 row in smem)
+cudaError_t launch_sparse_count(const float* x, int n, int pitch, int* row_nnz, unsigned long long* total, cudaStream_t s);
+cudaError_t launch_sparse_unit_steps(const int* row_nnz, int n, int lanes, unsigned int* unit_steps, int n_units, cudaStream_t s);
+cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsigned int* unit_off, cudaStream_t s);
+cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
+                               float* val, unsigned int* col2, cudaStream_t s);
+cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes, float* out, cudaStream_t s);
 
 }  // namespace dpsvm

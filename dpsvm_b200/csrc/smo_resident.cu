@@ -114,19 +114,27 @@ __device__ __forceinline__ int lru_lookup(const LruTable& t, int lines, int k, i
     return line;
 }
 
-template <int LPR, int ITERS>
+// SG == 0: the sweep reads the dense rows (LPR lanes per row, ITERS float4 chunks per lane).
+// SG  > 0: the sweep reads the sparse stream with SG lanes per row (SparseDev, smo_kernels.cuh); LPR and
+//          ITERS then only size the two selected-row buffers.  Everything outside the sweep is shared.
+template <int LPR, int ITERS, int SG>
 __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const ResidentDev a)
 {
-    constexpr int R = kRowsInFlight;
-    constexpr int GROUPS = 32 / LPR;
-    constexpr int RPW = GROUPS * R;
+    constexpr bool SPARSE = SG > 0;
+    constexpr int R = SPARSE ? 1 : kRowsInFlight;
+    constexpr int GROUPS = SPARSE ? 32 / (SPARSE ? SG : 1) : 32 / LPR;
+    constexpr int RPW = GROUPS * R;                    // rows per unit
     constexpr int CAP4 = LPR * ITERS;
     constexpr int NW = kResThreads / 32;
+    constexpr int SGL = SPARSE ? SG : 32;              // lanes per row in the sparse sweep
 
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     float4* s_hi = reinterpret_cast<float4*>(dyn_smem);
     float4* s_lo = s_hi + CAP4;
-    float4* s_x = s_lo + CAP4;                         // stationary rows [res_units * RPW][pitch4]
+    float4* s_x = s_lo + CAP4;                         // dense: stationary rows [res_units * RPW][pitch4]
+    // sparse: the pair interleaved, (x_hi[c], x_lo[c]), then the first step of each of this CTA's units
+    float2* s_hl = reinterpret_cast<float2*>(s_lo + CAP4);
+    unsigned int* s_uoff = reinterpret_cast<unsigned int*>(s_hl + CAP4 * 4);
     // their per-row scalars live on chip as well (a warp round on a stationary unit then touches no
     // global memory at all): |x|^2, y, f, alpha -- [a.res_units * RPW] each, after the rows
     float* s_rxsq = reinterpret_cast<float*>(s_x + (size_t)a.res_units * RPW * a.pitch4);
@@ -144,7 +152,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     __shared__ unsigned long long s_next_key[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int sub = lane % LPR, grp = lane / LPR;
+    const int sub = SPARSE ? lane % SGL : lane % LPR, grp = SPARSE ? lane / SGL : lane / LPR;
     const int G = gridDim.x, cta = blockIdx.x;
     DevState* st = a.st;
 
@@ -158,8 +166,11 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     long long cache_hits = st->cache_hits, cache_lookups = st->cache_lookups;
 
     const int n_units = (a.n + RPW - 1) / RPW;
-    const int u0 = (int)((long long)n_units * cta / G), u1 = (int)((long long)n_units * (cta + 1) / G);
-    const int res_units = min(u1 - u0, a.res_units);   // units kept in shared memory
+    // contiguous unit range of this CTA: equal unit counts (dense rows all cost the same), or the ranges
+    // the host balanced by steps (sparse rows differ in length)
+    const int u0 = SPARSE ? a.sp.cta_first[cta] : (int)((long long)n_units * cta / G);
+    const int u1 = SPARSE ? a.sp.cta_first[cta + 1] : (int)((long long)n_units * (cta + 1) / G);
+    const int res_units = SPARSE ? 0 : min(u1 - u0, a.res_units);   // units kept in shared memory
     const int us0 = u0 + res_units;                    // first streamed unit
 
     // the pair of the coming iteration (uniform over the CTA, identical in every CTA and every rank)
@@ -222,8 +233,12 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         a_hi_old = a.alpha[i_hi - a.index_base];
         a_lo_old = a.alpha[i_lo - a.index_base];
     }
-    // stationary slice -> shared memory; zero the tails of the two selected-row buffers once
-    {
+    if (SPARSE) {
+        for (int i = tid; i <= u1 - u0; i += kResThreads) s_uoff[i] = a.sp.unit_off[u0 + i];
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = a.pitch4 + tid; i < CAP4; i += kResThreads) { s_hi[i] = z; s_lo[i] = z; }
+    } else {
+        // stationary slice -> shared memory; zero the tails of the two selected-row buffers once
         const int total4 = res_units * RPW * a.pitch4;
         const float4* src = a.x4 + (size_t)u0 * RPW * a.pitch4;
         const long long valid4 = (long long)(a.n - (long long)u0 * RPW) * a.pitch4;     // rows past n do not exist
@@ -261,6 +276,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     const int my_units = u1 - u0;
     const int n_stream = my_units - res_units;
     float4 xv[R][ITERS];
+    SpChunk sp_nxt;                                    // sparse: the chunk in flight
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false, pre = false, unit_in_smem = false;
@@ -339,7 +355,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             const float* fl = reinterpret_cast<const float*>(s_lo);
             float part = 0.f;
             for (int i = tid; i < a.pitch4 * 4; i += kCtlThreads) {
-                const float df = __fsub_rn(fh[i], fl[i]);
+                const float vh = fh[i], vl = fl[i];
+                if (SPARSE) s_hl[i] = make_float2(vh, vl);
+                const float df = __fsub_rn(vh, vl);
                 part = __fmaf_rn(df, df, part);
             }
 #pragma unroll
@@ -426,6 +444,61 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             const int row_b = u0 * RPW, row_e = min(u1 * RPW, a.n);
             for (int row = row_b + tid; row < row_e; row += kResThreads)
                 epilogue(row, sc.line_hi[row], sc.line_lo[row], __ldg(a.xsq + row), a.f[row], a.alpha[row], __ldg(a.y + row), false);
+        } else if constexpr (SPARSE) {
+            // local unit k of this warp's sequence, forward or reverse; chunks of kSpChunk steps, one ahead
+            auto unit_of = [&](int k, bool rv) { return rv ? (my_units - 1 - k) : k; };
+            auto policy = [&](unsigned int beg) { return (beg - s_uoff[0]) < a.sp.pin_steps ? pol_keep : pol_stream; };
+            int k = warp;
+            unsigned int ubeg = 0;
+            int T = 0;
+            if (k < my_units) {
+                const int lu = unit_of(k, rev);
+                ubeg = s_uoff[lu];
+                T = (int)(s_uoff[lu + 1] - ubeg);
+                if (!pre) sp_load_chunk(sp_nxt, a.sp, ubeg, T, lane, policy(ubeg));
+            }
+            pre = false;
+            int t0 = 0;
+            float acc_hi = 0.f, acc_lo = 0.f;
+            while (k < my_units) {
+                const SpChunk cur = sp_nxt;
+                int k_n = k, t0_n = t0 + kSpChunk, T_n = T;
+                unsigned int ubeg_n = ubeg;
+                if (t0_n >= T) {
+                    k_n = k + NW;
+                    t0_n = 0;
+                    if (k_n < my_units) {
+                        const int lu = unit_of(k_n, rev);
+                        ubeg_n = s_uoff[lu];
+                        T_n = (int)(s_uoff[lu + 1] - ubeg_n);
+                    }
+                }
+                if (k_n < my_units) {
+                    sp_load_chunk(sp_nxt, a.sp, ubeg_n + (unsigned int)t0_n, T_n - t0_n, lane, policy(ubeg_n));
+                } else if (!last_iter) {
+                    // the stream does not depend on the pair: this warp's first chunk of the NEXT iteration (which
+                    // sweeps the other way) goes in flight now and lands during the barrier and the merge
+                    const int lu = unit_of(warp, !rev);
+                    const unsigned int b = s_uoff[lu];
+                    sp_load_chunk(sp_nxt, a.sp, b, (int)(s_uoff[lu + 1] - b), lane, policy(b));
+                    pre = true;
+                }
+                if (t0 == 0) {
+                    erow = (u0 + unit_of(k, rev)) * GROUPS + grp;
+                    eown = (sub == 0) && (erow < a.n);
+                    if (eown) {
+                        e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow);
+                        e_f = a.f[erow]; e_alpha = a.alpha[erow];
+                    }
+                }
+                sp_fma_chunk(cur, s_hl, acc_hi, acc_lo);
+                if (t0_n == 0) {
+                    sp_group_sum<SGL>(acc_hi, acc_lo);
+                    if (eown) epilogue(erow, acc_hi, acc_lo, e_xsq, e_f, e_alpha, e_y, true);
+                    acc_hi = 0.f; acc_lo = 0.f;
+                }
+                k = k_n; t0 = t0_n; ubeg = ubeg_n; T = T_n;
+            }
         } else {
             for (int k = warp; k < my_units; k += NW) {
                 if (!pre) load_const(k, rev);
@@ -468,7 +541,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         }
         // X does not depend on the pair: put the next iteration's first unit in flight now, so HBM keeps
         // streaming while the barrier, the slot merge and the eta reduction run
-        if (!last_iter && warp < my_units) { load_const(warp, !rev); pre = true; }
+        if constexpr (!SPARSE) {
+            if (!last_iter && warp < my_units) { load_const(warp, !rev); pre = true; }
+        }
 
         // ================= block best -> slot, grid barrier, merge =================
         __syncthreads();
@@ -560,7 +635,7 @@ static cudaError_t launch_resident_t(ResidentDev a, int variant, cudaStream_t s)
 {
     constexpr int RPW = (32 / LPR) * kRowsInFlight;
     constexpr int CAP4 = LPR * ITERS;
-    auto kernel = smo_resident_kernel<LPR, ITERS>;
+    auto kernel = smo_resident_kernel<LPR, ITERS, 0>;
     static int s_smem_max = -1, s_grid = 0;
     if (s_smem_max < 0) {
         int dev = 0, optin = 0;
@@ -629,6 +704,59 @@ static cudaError_t launch_resident_lpr(int iters, const ResidentDev& a, int vari
     return cudaErrorInvalidValue;
 }
 
+// Sparse sweep: the two selected-row buffers are sized for the widest supported row (LPR 32 x ITERS 8).
+template <int SG>
+static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStream_t s)
+{
+    constexpr int CAP4 = 256;
+    static_assert(CAP4 * 4 == kSparseMaxPitch, "selected-row buffers cover the widest sparse row");
+    auto kernel = smo_resident_kernel<32, 8, SG>;
+    static int s_smem_max = -1, s_grid = 0;
+    if (s_smem_max < 0) {
+        int dev = 0, optin = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        if (e != cudaSuccess) return e;
+        cudaFuncAttributes fa;
+        e = cudaFuncGetAttributes(&fa, kernel);
+        if (e != cudaSuccess) return e;
+        const int budget = optin - (int)fa.sharedSizeBytes - 1024;
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, budget);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kResThreads, 64 * 1024);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        s_grid = device_sm_count();
+        s_smem_max = budget;
+    }
+    if (a.sp.grid != s_grid) return cudaErrorInvalidValue;      // cta_first was balanced for another grid
+    const size_t smem = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + ((size_t)a.sp.max_cta_units + 1) * sizeof(unsigned int);
+    if (smem > (size_t)s_smem_max) return cudaErrorInvalidValue;
+    a.res_units = 0;
+    a.pin_units = 0;
+    const bool hint = (variant & 2) != 0;
+    a.stream_evict_first = hint ? 1 : 0;
+    a.sp.pin_steps = hint ? (unsigned int)(((double)((variant >> 8) & 0xFFFFF) * 1e6 / s_grid) / 192.0) : 0u;
+    a.parity0 = variant & 1;
+    void* args[] = {&a};
+    return cudaLaunchCooperativeKernel((void*)kernel, dim3((unsigned)s_grid), dim3(kResThreads), args, smem, s);
+}
+
+cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream_t s)
+{
+    switch (a.sp.lanes) {
+        case 4: return launch_resident_sparse_t<4>(a, variant, s);
+        case 8: return launch_resident_sparse_t<8>(a, variant, s);
+        case 16: return launch_resident_sparse_t<16>(a, variant, s);
+        case 32: return launch_resident_sparse_t<32>(a, variant, s);
+    }
+    return cudaErrorInvalidValue;
+}
+
+int resident_grid() { return device_sm_count(); }
+
 bool resident_supported(int pitch4, int cache_lines)
 {
     return pitch4 <= 256 && cache_lines <= kResCacheLines;
@@ -638,6 +766,7 @@ cudaError_t launch_resident(const ResidentDev& a, int variant, cudaStream_t s)
 {
     if (a.n <= 0) return cudaSuccess;
     if (!resident_supported(a.pitch4, a.cache_lines)) return cudaErrorInvalidValue;
+    if (a.sp.val) return launch_resident_sparse(a, variant, s);
     const DotGeom g = dot_geometry(a.pitch4);
     switch (g.lpr) {
         case 4: return launch_resident_lpr<4>(g.iters, a, variant, s);

@@ -1,0 +1,346 @@
+// smo_sparse.cu -- building the sparse stream of the owned rows at upload time (layout and summation
+// order: SparseDev in smo_kernels.cuh), and the decision whether a context sweeps it or the dense rows.
+//
+// The reference always multiplies dense rows (cublasSgemv over the whole shard, svmTrain.cu:222,247).
+// Its own data sets are mostly zeros -- convert_mnist_to_odd_even.py / convert_adult.py write them out as
+// dense CSV -- and the loop is bound by the bytes of X it re-reads every iteration, so the sweep reads
+// 6 B per non-zero instead of 4 B per cell when that is the smaller stream.  Zero terms add nothing to a
+// dot product; only the summation order of the non-zero terms differs from the dense kernels (both
+// orders are fixed and documented; the parity tests run both).
+#include <algorithm>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "dpsvm_internal.cuh"
+
+namespace dpsvm {
+
+#define CU(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess) return fail(e__ == cudaErrorMemoryAllocation ? DPSVM_ERR_NOMEM : DPSVM_ERR_CUDA, \
+                                            "%s -> %s", #call, cudaGetErrorString(e__));            \
+    } while (0)
+
+// ---- non-zeros per row (warp per row) and their total -------------------------------------------
+__global__ void __launch_bounds__(256) sparse_count_kernel(const float* __restrict__ x, int n, int pitch,
+                                                           int* __restrict__ row_nnz, unsigned long long* __restrict__ total)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    unsigned long long mine = 0;
+    for (int row = warp; row < n; row += n_warps) {
+        const float* rp = x + (size_t)row * pitch;
+        int cnt = 0;
+        for (int c0 = 0; c0 < pitch; c0 += 32) {
+            const float v = (c0 + lane < pitch) ? __ldg(rp + c0 + lane) : 0.f;
+            cnt += __popc(__ballot_sync(0xffffffffu, v != 0.f));
+        }
+        if (lane == 0) row_nnz[row] = cnt;
+        mine += (unsigned long long)cnt;
+    }
+    if (lane == 0 && mine) atomicAdd(total, mine);
+}
+
+// ---- steps per unit: the longest row of the unit over G lanes, rounded up to kSpStepAlign ----------
+__global__ void __launch_bounds__(256) sparse_unit_steps_kernel(const int* __restrict__ row_nnz, int n, int lanes,
+                                                                unsigned int* __restrict__ unit_steps, int n_units)
+{
+    const int groups = 32 / lanes;
+    for (int u = blockIdx.x * blockDim.x + threadIdx.x; u < n_units; u += gridDim.x * blockDim.x) {
+        int m = 0;
+        for (int r = 0; r < groups; ++r) {
+            const int row = u * groups + r;
+            if (row < n) m = max(m, row_nnz[row]);
+        }
+        const int steps = (m + lanes - 1) / lanes;
+        unit_steps[u] = (unsigned int)((steps + kSpStepAlign - 1) / kSpStepAlign * kSpStepAlign);
+    }
+}
+
+// ---- exclusive scan, one block (setup time; n_units is at most a few million) ----------------------
+__global__ void __launch_bounds__(1024, 1) sparse_scan_kernel(const unsigned int* __restrict__ in, int n, unsigned int* __restrict__ out)
+{
+    __shared__ unsigned int s_warp[32];
+    __shared__ unsigned int s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const unsigned int v = i < n ? in[i] : 0u;
+        unsigned int incl = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int w = s_warp[lane];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const unsigned int t = __shfl_up_sync(0xffffffffu, w, off);
+                if (lane >= off) w += t;
+            }
+            s_warp[lane] = w;           // inclusive over warps
+        }
+        __syncthreads();
+        const unsigned int before = s_carry + (warp ? s_warp[warp - 1] : 0u) + (incl - v);
+        if (i < n) out[i] = before;
+        __syncthreads();
+        if (tid == 1023) s_carry = before + v;
+        __syncthreads();
+    }
+    if (tid == 0) out[n] = s_carry;
+}
+
+// ---- fill: warp per row, ascending columns, entry e -> lane e % G of the row's group, step e / G -----
+__global__ void __launch_bounds__(256) sparse_fill_kernel(const float* __restrict__ x, int n, int pitch, int lanes,
+                                                          const unsigned int* __restrict__ unit_off,
+                                                          float* __restrict__ val, unsigned short* __restrict__ col_half)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    const int groups = 32 / lanes;
+    for (int row = warp; row < n; row += n_warps) {
+        const float* rp = x + (size_t)row * pitch;
+        const int unit = row / groups, grp = row % groups;
+        const unsigned int s0 = unit_off[unit];
+        int base = 0;
+        for (int c0 = 0; c0 < pitch; c0 += 32) {
+            const int col = c0 + lane;
+            const float v = (col < pitch) ? __ldg(rp + col) : 0.f;
+            const bool nz = v != 0.f;
+            const unsigned int mask = __ballot_sync(0xffffffffu, nz);
+            if (nz) {
+                const int e = base + __popc(mask & ((1u << lane) - 1u));
+                const unsigned int step = s0 + (unsigned int)(e / lanes);
+                const int slot = grp * lanes + (e % lanes);
+                val[(size_t)step * 32 + slot] = v;
+                col_half[((size_t)(step >> 1) * 32 + slot) * 2 + (step & 1u)] = (unsigned short)(col * 8);
+            }
+            base += __popc(mask);
+        }
+    }
+}
+
+// ---- |x_i|^2 in the sparse sweep's order, straight from the dense row ---------------------------------
+// Lane g < G plays the sweep's lane g: it squares the non-zeros e = g, g + G, ... in ascending order with
+// sequential FMAs; then the same xor-butterfly over the G lanes.
+template <int G>
+__global__ void __launch_bounds__(256) sparse_row_norms_kernel(const float* __restrict__ x, int n, int pitch, float* __restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (int row = warp; row < n; row += n_warps) {
+        const float* rp = x + (size_t)row * pitch;
+        float acc = 0.f;
+        int base = 0;
+        for (int c0 = 0; c0 < pitch; c0 += 32) {
+            const float v = (c0 + lane < pitch) ? __ldg(rp + c0 + lane) : 0.f;
+            const unsigned int mask = __ballot_sync(0xffffffffu, v != 0.f);
+            const int cnt = __popc(mask);
+            const int j0 = (lane - base) & (G - 1);        // first entry of this chunk that belongs to lane g
+#pragma unroll
+            for (int r = 0; r < 32 / G; ++r) {
+                const int j = j0 + r * G;
+                const bool ok = lane < G && j < cnt;
+                const unsigned int src = ok ? __fns(mask, 0, j + 1) : 0u;
+                const float w = __shfl_sync(0xffffffffu, v, (int)(src & 31u));
+                if (ok) acc = __fmaf_rn(w, w, acc);
+            }
+            base += cnt;
+        }
+        if (lane >= G) acc = 0.f;
+#pragma unroll
+        for (int off = G / 2; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
+        if (lane == 0) out[row] = acc;
+    }
+}
+
+static int warp_blocks(int n)
+{
+    int blocks = (n + 7) / 8;
+    const int cap = device_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    return blocks < 1 ? 1 : blocks;
+}
+
+cudaError_t launch_sparse_count(const float* x, int n, int pitch, int* row_nnz, unsigned long long* total, cudaStream_t s)
+{
+    cudaError_t e = cudaMemsetAsync(total, 0, sizeof(unsigned long long), s);
+    if (e != cudaSuccess || n <= 0) return e;
+    sparse_count_kernel<<<warp_blocks(n), 256, 0, s>>>(x, n, pitch, row_nnz, total);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sparse_unit_steps(const int* row_nnz, int n, int lanes, unsigned int* unit_steps, int n_units, cudaStream_t s)
+{
+    if (n_units <= 0) return cudaSuccess;
+    int blocks = (n_units + 255) / 256;
+    const int cap = device_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    sparse_unit_steps_kernel<<<blocks, 256, 0, s>>>(row_nnz, n, lanes, unit_steps, n_units);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsigned int* unit_off, cudaStream_t s)
+{
+    sparse_scan_kernel<<<1, 1024, 0, s>>>(unit_steps, n_units, unit_off);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
+                               float* val, unsigned int* col2, cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    sparse_fill_kernel<<<warp_blocks(n), 256, 0, s>>>(x, n, pitch, lanes, unit_off, val, reinterpret_cast<unsigned short*>(col2));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes, float* out, cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    const int blocks = warp_blocks(n);
+    switch (lanes) {
+        case 4: sparse_row_norms_kernel<4><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
+        case 8: sparse_row_norms_kernel<8><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
+        case 16: sparse_row_norms_kernel<16><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
+        case 32: sparse_row_norms_kernel<32><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-context setup: decide the layout, build the stream, compute the row norms in the matching order.
+// ------------------------------------------------------------------------------------------------
+void sparse_release(dpsvm_ctx* c)
+{
+    cudaFree(c->d_sp_val); cudaFree(c->d_sp_col2); cudaFree(c->d_sp_unit_off); cudaFree(c->d_sp_cta_first);
+    c->d_sp_val = nullptr; c->d_sp_col2 = nullptr; c->d_sp_unit_off = nullptr; c->d_sp_cta_first = nullptr;
+    c->sp = SparseDev{};
+    c->sp_nnz = -1;
+}
+
+constexpr double kSparseAutoRatio = 0.7;
+
+static int lanes_for(double mean_nnz)
+{
+    if (const char* v = getenv("DPSVM_SPARSE_LANES")) {
+        const int g = atoi(v);
+        if (g == 4 || g == 8 || g == 16 || g == 32) return g;
+    }
+    // measured at 60 000 x 784, 303 non-zeros per row: 4 and 8 lanes tie (27.5 / 27.2 us per iteration), 16 and 32
+    // lose to the per-row epilogue (32.5 / 56.7 us); short rows want few lanes so that a step is not mostly padding
+    return mean_nnz <= 32.0 ? 4 : 8;
+}
+
+// mode: 0 auto, 1 dense, 2 sparse (DPSVM_FLAG_DENSE / DPSVM_FLAG_SPARSE, or DPSVM_LAYOUT=dense|sparse|auto)
+static int layout_mode(const dpsvm_ctx* c)
+{
+    int mode = (c->p.flags & DPSVM_FLAG_DENSE) ? 1 : ((c->p.flags & DPSVM_FLAG_SPARSE) ? 2 : 0);
+    if (const char* v = getenv("DPSVM_LAYOUT")) {
+        if (!strcmp(v, "dense")) mode = 1;
+        else if (!strcmp(v, "sparse")) mode = 2;
+        else if (!strcmp(v, "auto")) mode = 0;
+    }
+    return mode;
+}
+
+int sparse_setup(dpsvm_ctx* c)
+{
+    sparse_release(c);
+    const int mode = layout_mode(c);
+    const int n = c->p.shard_rows, pitch = c->pitch;
+    const int off = c->p.shard_start - c->res0;
+    const float* x_own = c->d_x + (size_t)off * pitch;
+    cudaStream_t s = c->stream;
+    if (mode == 1 || pitch > kSparseMaxPitch) {
+        if (mode == 2) return fail(DPSVM_ERR_LIMIT, "sparse layout supports rows of at most %d floats (pitch %d)", kSparseMaxPitch, pitch);
+        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        return DPSVM_OK;
+    }
+    int* d_row_nnz = nullptr;
+    unsigned int* d_unit_steps = nullptr;
+    unsigned long long* d_total = nullptr;
+    struct Temps {
+        int*& a; unsigned int*& b; unsigned long long*& t;
+        ~Temps() { cudaFree(a); cudaFree(b); cudaFree(t); }
+    } temps{d_row_nnz, d_unit_steps, d_total};
+    CU(cudaMalloc(&d_row_nnz, sizeof(int) * (size_t)n));
+    CU(cudaMalloc(&d_total, sizeof(unsigned long long)));
+    CU(launch_sparse_count(x_own, n, pitch, d_row_nnz, d_total, s));
+    unsigned long long total = 0;
+    CU(cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    c->sp_nnz = (long long)total;
+    const double dense_bytes = 4.0 * (double)n * (double)c->p.num_attributes;
+    // auto: sparse when the stream is clearly the smaller one (6 B per non-zero plus padding against 4 B per cell).
+    // Measured at 60 000 x 784 with 38.7 % non-zeros: stream 117 MB vs 188 MB of dense rows, 27.2 vs 33.1 us per
+    // iteration; the sparse sweep sustains about three quarters of the dense sweep's byte rate, so the break-even
+    // is near 0.75 and the threshold sits a little below it.
+    if (mode == 0 && 6.0 * (double)total > kSparseAutoRatio * dense_bytes) {
+        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        return DPSVM_OK;
+    }
+    const int lanes = lanes_for((double)total / (double)n);
+    const int groups = 32 / lanes;
+    const int n_units = (n + groups - 1) / groups;
+    CU(cudaMalloc(&d_unit_steps, sizeof(unsigned int) * (size_t)n_units));
+    CU(cudaMalloc(&c->d_sp_unit_off, sizeof(unsigned int) * ((size_t)n_units + 1)));
+    CU(launch_sparse_unit_steps(d_row_nnz, n, lanes, d_unit_steps, n_units, s));
+    CU(launch_sparse_scan(d_unit_steps, n_units, c->d_sp_unit_off, s));
+    std::vector<unsigned int> h_off((size_t)n_units + 1);
+    CU(cudaMemcpyAsync(h_off.data(), c->d_sp_unit_off, sizeof(unsigned int) * h_off.size(), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const unsigned int total_steps = h_off[n_units];
+    const double stream_bytes = 192.0 * (double)total_steps;
+    if (mode == 0 && stream_bytes > kSparseAutoRatio * dense_bytes) {
+        sparse_release(c);
+        c->sp_nnz = (long long)total;
+        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        return DPSVM_OK;
+    }
+    const size_t val_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(float));
+    const size_t col_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(unsigned short));
+    CU(cudaMalloc(&c->d_sp_val, val_bytes));
+    CU(cudaMalloc(&c->d_sp_col2, col_bytes));
+    CU(cudaMemsetAsync(c->d_sp_val, 0, val_bytes, s));
+    CU(cudaMemsetAsync(c->d_sp_col2, 0, col_bytes, s));
+    CU(launch_sparse_fill(x_own, n, pitch, lanes, c->d_sp_unit_off, c->d_sp_val, c->d_sp_col2, s));
+    // resident loop: contiguous unit ranges per CTA, balanced by steps (rows differ in length)
+    const int grid = resident_grid();
+    std::vector<int> first((size_t)grid + 1);
+    int max_units = 0;
+    for (int i = 0; i <= grid; ++i) {
+        const unsigned long long target = (unsigned long long)total_steps * (unsigned long long)i / (unsigned long long)grid;
+        int u = (int)(std::lower_bound(h_off.begin(), h_off.end(), (unsigned int)target) - h_off.begin());
+        if (total_steps == 0) u = (int)((long long)n_units * i / grid);
+        if (u > n_units) u = n_units;
+        first[i] = u;
+    }
+    first[0] = 0; first[grid] = n_units;
+    for (int i = 0; i < grid; ++i) {
+        if (first[i + 1] < first[i]) first[i + 1] = first[i];
+        max_units = std::max(max_units, first[i + 1] - first[i]);
+    }
+    CU(cudaMalloc(&c->d_sp_cta_first, sizeof(int) * first.size()));
+    CU(cudaMemcpyAsync(c->d_sp_cta_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice, s));
+    CU(launch_sparse_row_norms(c->d_x, c->res_n, pitch, lanes, c->d_xsq, s));
+    CU(cudaStreamSynchronize(s));       // `first` is pageable and goes out of scope
+    SparseDev sp{};
+    sp.val = c->d_sp_val; sp.col2 = c->d_sp_col2; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
+    sp.lanes = lanes; sp.n_units = n_units; sp.grid = grid; sp.max_cta_units = max_units;
+    sp.total_steps = total_steps; sp.pin_steps = 0;
+    c->sp = sp;
+    return DPSVM_OK;
+}
+
+}  // namespace dpsvm

@@ -162,6 +162,12 @@ typedef struct {
 #define DPSVM_FLAG_X_SHARD_ONLY 2    /* dpsvm_upload receives / keeps only the owned rows of X */
 #define DPSVM_FLAG_GRAPH_LOOP 4      /* run the loop as a CUDA graph of [control, pass] kernel pairs instead of the
                                         resident (persistent, cooperative) kernel; results are identical */
+#define DPSVM_FLAG_DENSE 8           /* the sweep always reads the dense rows (what the reference's cublasSgemv does,
+                                        svmTrain.cu:222,247) */
+#define DPSVM_FLAG_SPARSE 16         /* the sweep always reads the sparse stream of the owned rows (rows of at most
+                                        1024 floats).  Neither flag: decided per upload from the share of non-zeros.
+                                        The two layouts add the same non-zero products in a different, fixed order
+                                        (see dpsvm_layout_info); results agree to fp32 rounding of the dot products. */
 
 int dpsvm_create(const dpsvm_params* params, dpsvm_ctx** out);
 int dpsvm_destroy(dpsvm_ctx* ctx);
@@ -220,6 +226,17 @@ int dpsvm_train_async(dpsvm_ctx* ctx, int iters);
 int dpsvm_loop_info(dpsvm_ctx* ctx, int* resident, int* chunk);
 int dpsvm_sync(dpsvm_ctx* ctx, dpsvm_train_status* status);
 void* dpsvm_stream(dpsvm_ctx* ctx);
+/* What the per-iteration sweep reads on this context (decided by the last upload).  No reference counterpart:
+ * the reference multiplies dense rows whatever the data (svmTrain.cu:222,247), although the data sets it was
+ * measured on are 80-90 % zeros (convert_mnist_to_odd_even.py, convert_adult.py).
+ *   *lanes        0: dense rows, dot products in the order of dpsvm_row_norms;
+ *                 4/8/16/32: the sparse stream -- the non-zeros of a row in ascending column order are dealt
+ *                 round-robin to that many lanes, each lane adds its products with sequential FMAs, an
+ *                 xor-butterfly sums the lanes; |x|^2 is summed in the same order.
+ *   *nnz          non-zeros of the owned rows (-1 when they were not counted: dense layout forced or rows too wide)
+ *   *sweep_bytes  bytes of X (or of its sparse stream) one sweep reads, padding included.
+ * Outputs may be NULL. */
+int dpsvm_layout_info(dpsvm_ctx* ctx, int* lanes, long long* nnz, long long* sweep_bytes);
 
 /* Copy state back: global alpha of the owned rows (the caller-side alpha[] of
  * svmTrainMain.cpp:223,298-299), f, and |x|^2. Each may be NULL. */

@@ -40,7 +40,7 @@ def test_noalloc_iteration_matches_trainer_context(golden):
     capi.select(dalpha, dy, df, n, c, 0, dkeys)
     torch.cuda.synchronize()
 
-    with capi.Trainer(n, d, c, gamma, eps, cache_size=0) as t:      # the existing entry points
+    with capi.Trainer(n, d, c, gamma, eps, cache_size=0, flags=capi.FLAG_DENSE) as t:      # the existing entry points (dense sweep, as the no-alloc call)
         t.upload(x, y)
         for call in range(2):                                        # two calls in a row
             st = t.train(1)
