@@ -487,7 +487,10 @@ static int finish_upload(dpsvm_ctx* c)
     if (!getenv("DPSVM_VARIANT")) {
         // L2 policy follows what the sweep actually reads: hints and a pinned prefix once that outgrows L2
         const double mb = c->sp.val ? 192e-6 * (double)c->sp.total_steps : 4e-6 * (double)c->p.shard_rows * (double)c->pitch;
-        c->variant = mb > 64.0 ? (2 | (32 << 8)) : 0;
+        // a stream about the size of L2 is kept there whole (measured at 123 MB: 25.9 us per iteration with 120 MB
+        // pinned, 27.2 with 96, 28.3 with 64); a larger one keeps a 32 MB prefix (profiles/r01_l2_sweep.md)
+        const int pin_mb = (c->sp.val && mb <= 130.0) ? 120 : 32;
+        c->variant = mb > 64.0 ? (2 | (pin_mb << 8)) : 0;
     }
     c->uploaded = true;
     return reset_state(c);

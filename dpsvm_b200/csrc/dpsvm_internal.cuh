@@ -39,7 +39,7 @@ struct dpsvm_ctx {
     // sparse stream of the owned rows (smo_sparse.cu); sp.val == null: the sweep reads the dense rows
     dpsvm::SparseDev sp{};
     float* d_sp_val = nullptr;
-    unsigned int* d_sp_col2 = nullptr;
+    unsigned short* d_sp_col = nullptr;
     unsigned int* d_sp_unit_off = nullptr;
     int* d_sp_cta_first = nullptr;
     long long sp_nnz = -1;       // non-zeros of the owned rows (-1: not counted, dense layout forced)

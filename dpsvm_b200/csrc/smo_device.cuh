@@ -74,53 +74,62 @@ __device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
 // ------------------------------------------------------------------------------------------------
 // Sparse sweep building blocks (layout and order: SparseDev in smo_kernels.cuh).
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float ldg_f32_pol(const float* p, uint64_t pol)
-{
-    float v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
-    return v;
-}
-__device__ __forceinline__ unsigned int ldg_u32_pol(const unsigned int* p, uint64_t pol)
-{
-    unsigned int v;
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
-    return v;
-}
+struct SpBuf {               // one chunk of kSpChunk steps for this lane
+    unsigned int v[kSpChunk];   // fp32 bit patterns, exactly as the 256-bit load leaves them (no register moves)
+    uint4 c;                 // 8 x 16-bit byte offsets into the interleaved (x_hi, x_lo) row
+};
+static_assert(kSpChunk == 8, "a chunk is one 256-bit value load and one 128-bit offset load per lane");
 
-struct SpChunk {
-    float v[kSpChunk];
-    unsigned int c2[kSpChunk / 2];
+// 256-bit loads carry their L2 eviction priority in the opcode (LDG.E.NA.ELL2.256 / .EFL2.256): no policy
+// register, no R2UR.  keep: 1 evict_last, 0 evict_first, -1 evict_normal.
+// Chunks [chunk0, chunk0 + n) of the stream held in shared memory for the whole launch (resident loop): values
+// as [chunk][half][lane] float4 (conflict-free 128-bit reads), offsets as [chunk][lane] uint4.
+struct SpRes {
+    unsigned int chunk0, n;
+    const float4* val;
+    const uint4* col;
 };
 
-// Steps [step0, step0 + min(steps_left, kSpChunk)) of a unit for this lane; step0 is even.  What lies past
-// the unit's end is value 0 / offset 0: an FMA with it leaves the accumulators as they are.
-__device__ __forceinline__ void sp_load_chunk(SpChunk& ch, const SparseDev& sp, unsigned int step0, int steps_left,
-                                              int lane, uint64_t pol)
+__device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpRes& res, unsigned int chunk, int lane, int keep, uint64_t pol)
 {
-    const float* vp = sp.val + (size_t)step0 * 32 + lane;
-    const unsigned int* cp = sp.col2 + (size_t)(step0 >> 1) * 32 + lane;
-#pragma unroll
-    for (int j = 0; j < kSpChunk; j += 2) {
-        const bool ok = j < steps_left;             // steps come in pairs (kSpStepAlign == 2)
-        ch.v[j] = ok ? ldg_f32_pol(vp + j * 32, pol) : 0.f;
-        ch.v[j + 1] = ok ? ldg_f32_pol(vp + (j + 1) * 32, pol) : 0.f;
-        ch.c2[j / 2] = ok ? ldg_u32_pol(cp + (j / 2) * 32, pol) : 0u;
+    const unsigned int rc = chunk - res.chunk0;
+    if (rc < res.n) {
+        const float4 lo = res.val[(rc * 2 + 0) * 32 + lane], hi = res.val[(rc * 2 + 1) * 32 + lane];
+        b.v[0] = __float_as_uint(lo.x); b.v[1] = __float_as_uint(lo.y); b.v[2] = __float_as_uint(lo.z); b.v[3] = __float_as_uint(lo.w);
+        b.v[4] = __float_as_uint(hi.x); b.v[5] = __float_as_uint(hi.y); b.v[6] = __float_as_uint(hi.z); b.v[7] = __float_as_uint(hi.w);
+        b.c = res.col[rc * 32 + lane];
+        return;
     }
+    const float* vp = sp.val + ((size_t)chunk * 32 + lane) * kSpChunk;
+    const uint4* cp = reinterpret_cast<const uint4*>(sp.col) + (size_t)chunk * 32 + lane;
+    if (keep > 0) {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+    } else if (keep == 0) {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_normal.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+    }
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol));
 }
 
-// s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]); c2 holds BYTE offsets into it.
-__device__ __forceinline__ void sp_fma_chunk(const SpChunk& ch, const float2* s_hl, float& acc_hi, float& acc_lo)
+// s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]); the offsets are BYTE offsets into it.
+__device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float& acc_hi, float& acc_lo)
 {
     const unsigned char* base = reinterpret_cast<const unsigned char*>(s_hl);
+    const unsigned int w[4] = {b.c.x, b.c.y, b.c.z, b.c.w};
 #pragma unroll
-    for (int j = 0; j < kSpChunk; j += 2) {
-        const unsigned int w = ch.c2[j / 2];
-        const float2 h0 = *reinterpret_cast<const float2*>(base + (w & 0xFFFFu));
-        const float2 h1 = *reinterpret_cast<const float2*>(base + (w >> 16));
-        acc_hi = __fmaf_rn(ch.v[j], h0.x, acc_hi);
-        acc_lo = __fmaf_rn(ch.v[j], h0.y, acc_lo);
-        acc_hi = __fmaf_rn(ch.v[j + 1], h1.x, acc_hi);
-        acc_lo = __fmaf_rn(ch.v[j + 1], h1.y, acc_lo);
+    for (int j = 0; j < 4; ++j) {
+        const float2 h0 = *reinterpret_cast<const float2*>(base + (w[j] & 0xFFFFu));
+        const float2 h1 = *reinterpret_cast<const float2*>(base + (w[j] >> 16));
+        const float v0 = __uint_as_float(b.v[2 * j]), v1 = __uint_as_float(b.v[2 * j + 1]);
+        acc_hi = __fmaf_rn(v0, h0.x, acc_hi);
+        acc_lo = __fmaf_rn(v0, h0.y, acc_lo);
+        acc_hi = __fmaf_rn(v1, h1.x, acc_hi);
+        acc_lo = __fmaf_rn(v1, h1.y, acc_lo);
     }
 }
 
@@ -131,6 +140,121 @@ __device__ __forceinline__ void sp_group_sum(float& acc_hi, float& acc_lo)
     for (int off = G / 2; off >= 1; off >>= 1) {
         acc_hi = __fadd_rn(acc_hi, __shfl_xor_sync(0xffffffffu, acc_hi, off));
         acc_lo = __fadd_rn(acc_lo, __shfl_xor_sync(0xffffffffu, acc_lo, off));
+    }
+}
+
+// A warp's position in its chunk sequence: sequence unit k (k_first, k_first + k_stride, ... < k_end), chunk c of
+// the unit's nc chunks.  SEQ supplies  void unit(int k, unsigned int& first_step, int& steps)  and the L2 policy
+// int keep(unsigned int first_step).
+struct SpCursor {
+    int k, c, nc;
+    unsigned int chunk0;
+    int keep;
+};
+template <class SEQ>
+__device__ __forceinline__ void sp_open(SpCursor& q, const SEQ& seq)
+{
+    q.c = 0;
+    if (q.k < seq.k_end) {
+        unsigned int beg;
+        int steps;
+        seq.unit(q.k, beg, steps);
+        q.chunk0 = beg / kSpChunk;
+        q.nc = steps / kSpChunk;
+        q.keep = seq.keep(beg);
+    }
+}
+template <class SEQ>
+__device__ __forceinline__ void sp_next(SpCursor& q, const SEQ& seq)
+{
+    if (++q.c >= q.nc) { q.k += seq.k_stride; sp_open(q, seq); }
+}
+
+// Resident loop: local units of one CTA, first steps in shared memory, forward or reverse.
+struct SpSeqCta {
+    int k_first, k_stride, k_end;       // k_end = units of this CTA
+    const unsigned int* uoff;           // [k_end + 1] in shared memory
+    bool rev;
+    int hint;                           // 0: no eviction hints at all
+    unsigned int pin_steps;             // steps of the CTA's range (from its start) kept in L2
+    __device__ __forceinline__ int local(int k) const { return rev ? (k_end - 1 - k) : k; }
+    __device__ __forceinline__ void unit(int k, unsigned int& beg, int& steps) const
+    {
+        const int lu = local(k);
+        beg = uoff[lu];
+        steps = (int)(uoff[lu + 1] - beg);
+    }
+    __device__ __forceinline__ int keep(unsigned int beg) const { return hint ? ((beg - uoff[0]) < pin_steps ? 1 : 0) : -1; }
+};
+// Graph loop: units of the whole shard, first steps in global memory.
+struct SpSeqGrid {
+    int k_first, k_stride, k_end;       // k_end = units of the shard
+    const unsigned int* unit_off;
+    bool rev;
+    int hint;
+    unsigned int pin_steps;
+    __device__ __forceinline__ int local(int k) const { return rev ? (k_end - 1 - k) : k; }
+    __device__ __forceinline__ void unit(int k, unsigned int& beg, int& steps) const
+    {
+        const int u = local(k);
+        beg = __ldg(unit_off + u);
+        steps = (int)(__ldg(unit_off + u + 1) - beg);
+    }
+    __device__ __forceinline__ int keep(unsigned int beg) const { return hint ? (beg < pin_steps ? 1 : 0) : -1; }
+};
+
+// Put the first kSpRing chunks of a sequence in flight (ring slots 0 ..), e.g. for the NEXT iteration while the
+// barrier and the merge of this one run.
+template <class SEQ>
+__device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, int lane, uint64_t pol_keep, uint64_t pol_stream)
+{
+    SpCursor p;
+    p.k = seq.k_first;
+    sp_open(p, seq);
+#pragma unroll
+    for (int b = 0; b < kSpRing; ++b) {
+        if (p.k < seq.k_end) {
+            sp_load(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep > 0 ? pol_keep : pol_stream);
+            sp_next(p, seq);
+        }
+    }
+}
+
+// The sweep of one warp over its sequence.  The first kSpRing chunks are already in flight (sp_prefetch); every
+// consumed slot is refilled at once with the chunk kSpRing ahead.  (Measured: rings of 2, 3, 4 and 6 chunks run
+// at the same speed -- the sweep is bound by the shared-memory gathers, not by loads in flight.)  begin(k) runs when a unit starts (row scalars), end(k, dot_hi, dot_lo) after its last chunk, with the
+// G-lane sums done.
+template <int G, class SEQ, class BEGIN, class END>
+__device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, const float2* s_hl, int lane,
+                                         uint64_t pol_keep, uint64_t pol_stream, BEGIN begin, END end)
+{
+    SpCursor cns, prd;
+    cns.k = seq.k_first;
+    sp_open(cns, seq);
+    prd = cns;
+#pragma unroll
+    for (int b = 0; b < kSpRing; ++b) if (prd.k < seq.k_end) sp_next(prd, seq);
+    float acc_hi = 0.f, acc_lo = 0.f;
+    bool more = cns.k < seq.k_end;
+    while (more) {
+#pragma unroll
+        for (int b = 0; b < kSpRing; ++b) {
+            if (more) {
+                if (cns.c == 0) begin(cns.k);
+                sp_fma(ring[b], s_hl, acc_hi, acc_lo);
+                if (cns.c + 1 >= cns.nc) {
+                    sp_group_sum<G>(acc_hi, acc_lo);
+                    end(cns.k, acc_hi, acc_lo);
+                    acc_hi = 0.f; acc_lo = 0.f;
+                }
+                sp_next(cns, seq);
+                more = cns.k < seq.k_end;
+                if (prd.k < seq.k_end) {
+                    sp_load(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep > 0 ? pol_keep : pol_stream);
+                    sp_next(prd, seq);
+                }
+            }
+        }
     }
 }
 

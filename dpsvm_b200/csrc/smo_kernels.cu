@@ -359,32 +359,25 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sub = lane % G, grp = lane / G;
-    const int n_units = a.sp.n_units;
-    const int unit_stride = gridDim.x * (kPassThreads / 32);
 
     uint64_t pol_keep, pol_stream;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
     if (a.sp.pin_steps) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
     else asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol_stream));
 
-    int unit = blockIdx.x * (kPassThreads / 32) + warp;
-    SpChunk nxt;
-    unsigned int ubeg = 0;
-    int T = 0;
-    auto open_unit = [&](int k, unsigned int& beg, int& steps) {
-        const int u = a.reverse ? (n_units - 1 - k) : k;
-        beg = __ldg(a.sp.unit_off + u);
-        steps = (int)(__ldg(a.sp.unit_off + u + 1) - beg);
-    };
-    auto policy = [&](unsigned int beg) { return beg < a.sp.pin_steps ? pol_keep : pol_stream; };
+    SpSeqGrid seq;
+    seq.k_first = blockIdx.x * (kPassThreads / 32) + warp;
+    seq.k_stride = gridDim.x * (kPassThreads / 32);
+    seq.k_end = a.sp.n_units;
+    seq.unit_off = a.sp.unit_off;
+    seq.rev = a.reverse != 0;
+    seq.hint = a.sp.pin_steps != 0;
+    seq.pin_steps = a.sp.pin_steps;
 
-    // the stream does not depend on the pair: first chunk in flight before the dependency wait
-    bool loaded = false;
-    if (a.early_load && unit < n_units) {
-        open_unit(unit, ubeg, T);
-        sp_load_chunk(nxt, a.sp, ubeg, T, lane, policy(ubeg));
-        loaded = true;
-    }
+    // the stream does not depend on the pair: first chunks in flight before the dependency wait
+    SpBuf ring[kSpRing];
+    const SpRes res{0u, 0u, nullptr, nullptr};      // nothing is kept on chip across kernel launches
+    if (a.early_load) sp_prefetch(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
@@ -405,44 +398,23 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
         s_hl[4 * i + 3] = make_float2(h.w, l.w);
     }
     __syncthreads();
+    if (!a.early_load) sp_prefetch(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
 
-    if (unit < n_units && !loaded) {
-        open_unit(unit, ubeg, T);
-        sp_load_chunk(nxt, a.sp, ubeg, T, lane, policy(ubeg));
-    }
-    int t0 = 0;
-    float acc_hi = 0.f, acc_lo = 0.f;
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false;
-    while (unit < n_units) {
-        const SpChunk cur = nxt;
-        int unit_n = unit, t0_n = t0 + kSpChunk;
-        unsigned int ubeg_n = ubeg;
-        int T_n = T;
-        if (t0_n >= T) {
-            unit_n = unit + unit_stride;
-            t0_n = 0;
-            if (unit_n < n_units) open_unit(unit_n, ubeg_n, T_n);
-        }
-        if (unit_n < n_units) sp_load_chunk(nxt, a.sp, ubeg_n + (unsigned int)t0_n, T_n - t0_n, lane, policy(ubeg_n));
-        if (t0 == 0) {
-            const int u = a.reverse ? (n_units - 1 - unit) : unit;
-            erow = u * GROUPS + grp;
+    sp_sweep<G>(ring, a.sp, res, seq, s_hl, lane, pol_keep, pol_stream,
+        [&](int k) {
+            erow = seq.local(k) * GROUPS + grp;
             eown = (sub == 0) && (erow < a.n);
             if (eown) {
                 e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow);
                 e_f = a.f[erow]; e_alpha = a.alpha[erow];
             }
-        }
-        sp_fma_chunk(cur, s_hl, acc_hi, acc_lo);
-        if (t0_n == 0) {
-            sp_group_sum<G>(acc_hi, acc_lo);
-            if (eown) row_epilogue(erow, acc_hi, acc_lo, e_xsq, e_f, e_alpha, e_y, sc, a, true, best_up, best_low);
-            acc_hi = 0.f; acc_lo = 0.f;
-        }
-        unit = unit_n; t0 = t0_n; ubeg = ubeg_n; T = T_n;
-    }
+        },
+        [&](int, float dh, float dl) {
+            if (eown) row_epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, sc, a, true, best_up, best_low);
+        });
     publish_keys(best_up, best_low, a.keys, s_red);
     push_if_last(a.push, &s_pushflag);
 }

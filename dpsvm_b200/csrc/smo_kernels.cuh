@@ -21,21 +21,22 @@ struct PushDev;
 // Layout ("sliced ELL", slices of 32/G rows, G lanes per row):  a UNIT is 32/G consecutive rows; row
 // r of the unit belongs to lane group r.  The non-zeros of a row, in ascending column order, are dealt
 // round-robin to the G lanes of its group: entry e goes to lane e % G, step e / G.  A unit has
-// T = unit_off[u+1] - unit_off[u] steps (the longest row of the unit, rounded up to kSpStepAlign;
-// shorter rows are padded with value 0 / column 0, which leave an FMA accumulator unchanged).  Step t
-// of the unit is 32 values  val[(unit_off[u] + t) * 32 + lane]  -- one coalesced 128 B load per warp --
-// and the byte offsets (8 * column, into the interleaved (x_hi, x_lo) float2 row in shared memory)
-// of two consecutive steps share one 32-bit word:  col2[((unit_off[u] + t) / 2) * 32 + lane].
+// T = unit_off[u+1] - unit_off[u] steps: the longest row of the unit, rounded up to a whole number of
+// CHUNKS of kSpChunk = 8 steps (at least one); shorter rows are padded with value 0 / column 0, which
+// leave an FMA accumulator unchanged.  Chunk q of the stream is, for each of the 32 lanes, 8 consecutive
+// values  val[(q * 32 + lane) * 8 + i]  -- one 256-bit load per lane, 1 KB per warp -- and 8 16-bit byte
+// offsets  col[(q * 32 + lane) * 8 + i] = 8 * column  into the interleaved (x_hi, x_lo) float2 row in
+// shared memory -- one 128-bit load per lane.
 //
 // Dot-product order of the sparse layout (the counterpart of DotGeom): per lane sequential FMAs over
 // its entries in step order, then an xor-butterfly over the G lanes.  The row norms of a sparse
 // context are summed in the same order (sparse_row_norms), so <x_i,x_i> == |x_i|^2 stays bit-exact.
 // ------------------------------------------------------------------------------------------------
-constexpr int kSpStepAlign = 2;
-constexpr int kSpChunk = 16;            // steps per register chunk (one chunk ahead is in flight)
+constexpr int kSpChunk = 8;             // steps per chunk = alignment of a unit's step count
+constexpr int kSpRing = 2;              // register chunks per warp: one being consumed, one in flight
 struct SparseDev {
     const float* val;           // null: dense sweep
-    const unsigned int* col2;
+    const unsigned short* col;
     const unsigned int* unit_off;   // [n_units + 1] first step of each unit
     const int* cta_first;       // [grid + 1] first unit of each CTA of the resident loop (balanced by steps)
     int lanes;                  // G: 4, 8, 16 or 32
@@ -44,6 +45,7 @@ struct SparseDev {
     int max_cta_units;          // largest cta_first[i+1] - cta_first[i]
     unsigned int total_steps;
     unsigned int pin_steps;     // filled by the launcher: steps per CTA loaded L2::evict_last
+    unsigned int res_chunks;    // filled by the launcher (resident loop): chunks per CTA kept in shared memory
 };
 
 // Arguments of the fused pass kernel (by value; small enough for the parameter space).
@@ -229,7 +231,7 @@ cudaError_t launch_sparse_count(const float* x, int n, int pitch, int* row_nnz, 
 cudaError_t launch_sparse_unit_steps(const int* row_nnz, int n, int lanes, unsigned int* unit_steps, int n_units, cudaStream_t s);
 cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsigned int* unit_off, cudaStream_t s);
 cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
-                               float* val, unsigned int* col2, cudaStream_t s);
+                               float* val, unsigned short* col, cudaStream_t s);
 cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes, float* out, cudaStream_t s);
 
 }  // namespace dpsvm

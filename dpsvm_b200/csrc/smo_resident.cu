@@ -28,6 +28,7 @@
 //     decision.
 //   * Multi-GPU: after the local barrier CTA 0 stores the rank's candidate package into every peer's
 //     mailbox over NVLink; every CTA then waits on the arrival flags and merges the packages itself.
+#include <algorithm>
 #include <limits.h>
 #include <math.h>
 #include <stdlib.h>
@@ -135,6 +136,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     // sparse: the pair interleaved, (x_hi[c], x_lo[c]), then the first step of each of this CTA's units
     float2* s_hl = reinterpret_cast<float2*>(s_lo + CAP4);
     unsigned int* s_uoff = reinterpret_cast<unsigned int*>(s_hl + CAP4 * 4);
+    // ... then the first chunks of this CTA's part of the stream, kept on chip for the whole launch
+    float4* s_rval = reinterpret_cast<float4*>(s_uoff + ((a.sp.max_cta_units + 1 + 3) & ~3));
+    uint4* s_rcol = reinterpret_cast<uint4*>(s_rval + (size_t)a.sp.res_chunks * 64);
     // their per-row scalars live on chip as well (a warp round on a stationary unit then touches no
     // global memory at all): |x|^2, y, f, alpha -- [a.res_units * RPW] each, after the rows
     float* s_rxsq = reinterpret_cast<float*>(s_x + (size_t)a.res_units * RPW * a.pitch4);
@@ -233,8 +237,19 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         a_hi_old = a.alpha[i_hi - a.index_base];
         a_lo_old = a.alpha[i_lo - a.index_base];
     }
+    SpRes sp_res{0u, 0u, s_rval, s_rcol};
     if (SPARSE) {
         for (int i = tid; i <= u1 - u0; i += kResThreads) s_uoff[i] = a.sp.unit_off[u0 + i];
+        const unsigned int c_first = a.sp.unit_off[u0] / kSpChunk, c_end = a.sp.unit_off[u1] / kSpChunk;
+        sp_res.chunk0 = c_first;
+        sp_res.n = min(c_end - c_first, a.sp.res_chunks);
+        const float4* gv = reinterpret_cast<const float4*>(a.sp.val) + (size_t)c_first * 64;      // [chunk][lane][2 x float4]
+        const uint4* gc = reinterpret_cast<const uint4*>(a.sp.col) + (size_t)c_first * 32;
+        for (unsigned int i = tid; i < sp_res.n * 64u; i += kResThreads) {
+            const unsigned int rc = i >> 6, half = (i >> 5) & 1u, ln = i & 31u;
+            s_rval[i] = ldg_stream4(gv + (size_t)(rc * 32u + ln) * 2u + half);
+        }
+        for (unsigned int i = tid; i < sp_res.n * 32u; i += kResThreads) s_rcol[i] = __ldg(gc + i);
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int i = a.pitch4 + tid; i < CAP4; i += kResThreads) { s_hi[i] = z; s_lo[i] = z; }
     } else {
@@ -276,7 +291,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     const int my_units = u1 - u0;
     const int n_stream = my_units - res_units;
     float4 xv[R][ITERS];
-    SpChunk sp_nxt;                                    // sparse: the chunk in flight
+    SpBuf sp_ring[kSpRing];                            // sparse: the chunks in flight
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false, pre = false, unit_in_smem = false;
@@ -445,59 +460,32 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             for (int row = row_b + tid; row < row_e; row += kResThreads)
                 epilogue(row, sc.line_hi[row], sc.line_lo[row], __ldg(a.xsq + row), a.f[row], a.alpha[row], __ldg(a.y + row), false);
         } else if constexpr (SPARSE) {
-            // local unit k of this warp's sequence, forward or reverse; chunks of kSpChunk steps, one ahead
-            auto unit_of = [&](int k, bool rv) { return rv ? (my_units - 1 - k) : k; };
-            auto policy = [&](unsigned int beg) { return (beg - s_uoff[0]) < a.sp.pin_steps ? pol_keep : pol_stream; };
-            int k = warp;
-            unsigned int ubeg = 0;
-            int T = 0;
-            if (k < my_units) {
-                const int lu = unit_of(k, rev);
-                ubeg = s_uoff[lu];
-                T = (int)(s_uoff[lu + 1] - ubeg);
-                if (!pre) sp_load_chunk(sp_nxt, a.sp, ubeg, T, lane, policy(ubeg));
-            }
+            SpSeqCta seq;
+            seq.k_first = warp; seq.k_stride = NW; seq.k_end = my_units;
+            seq.uoff = s_uoff;
+            seq.rev = rev;
+            seq.hint = a.stream_evict_first;
+            seq.pin_steps = a.sp.pin_steps;
+            if (!pre) sp_prefetch(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
             pre = false;
-            int t0 = 0;
-            float acc_hi = 0.f, acc_lo = 0.f;
-            while (k < my_units) {
-                const SpChunk cur = sp_nxt;
-                int k_n = k, t0_n = t0 + kSpChunk, T_n = T;
-                unsigned int ubeg_n = ubeg;
-                if (t0_n >= T) {
-                    k_n = k + NW;
-                    t0_n = 0;
-                    if (k_n < my_units) {
-                        const int lu = unit_of(k_n, rev);
-                        ubeg_n = s_uoff[lu];
-                        T_n = (int)(s_uoff[lu + 1] - ubeg_n);
-                    }
-                }
-                if (k_n < my_units) {
-                    sp_load_chunk(sp_nxt, a.sp, ubeg_n + (unsigned int)t0_n, T_n - t0_n, lane, policy(ubeg_n));
-                } else if (!last_iter) {
-                    // the stream does not depend on the pair: this warp's first chunk of the NEXT iteration (which
-                    // sweeps the other way) goes in flight now and lands during the barrier and the merge
-                    const int lu = unit_of(warp, !rev);
-                    const unsigned int b = s_uoff[lu];
-                    sp_load_chunk(sp_nxt, a.sp, b, (int)(s_uoff[lu + 1] - b), lane, policy(b));
-                    pre = true;
-                }
-                if (t0 == 0) {
-                    erow = (u0 + unit_of(k, rev)) * GROUPS + grp;
+            sp_sweep<SGL>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
+                [&](int k) {
+                    erow = (u0 + seq.local(k)) * GROUPS + grp;
                     eown = (sub == 0) && (erow < a.n);
                     if (eown) {
                         e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow);
                         e_f = a.f[erow]; e_alpha = a.alpha[erow];
                     }
-                }
-                sp_fma_chunk(cur, s_hl, acc_hi, acc_lo);
-                if (t0_n == 0) {
-                    sp_group_sum<SGL>(acc_hi, acc_lo);
-                    if (eown) epilogue(erow, acc_hi, acc_lo, e_xsq, e_f, e_alpha, e_y, true);
-                    acc_hi = 0.f; acc_lo = 0.f;
-                }
-                k = k_n; t0 = t0_n; ubeg = ubeg_n; T = T_n;
+                },
+                [&](int, float dh, float dl) {
+                    if (eown) epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, true);
+                });
+            // the stream does not depend on the pair: this warp's first chunks of the NEXT iteration (which sweeps
+            // the other way) go in flight now and land during the barrier and the merge
+            if (!last_iter) {
+                seq.rev = !rev;
+                sp_prefetch(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
+                pre = true;
             }
         } else {
             for (int k = warp; k < my_units; k += NW) {
@@ -732,8 +720,17 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
         s_smem_max = budget;
     }
     if (a.sp.grid != s_grid) return cudaErrorInvalidValue;      // cta_first was balanced for another grid
-    const size_t smem = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + ((size_t)a.sp.max_cta_units + 1) * sizeof(unsigned int);
-    if (smem > (size_t)s_smem_max) return cudaErrorInvalidValue;
+    const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int);
+    if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;
+    // the rest of shared memory holds the head of each CTA's part of the stream (1.5 KB per chunk)
+    size_t res_bytes = (size_t)s_smem_max - fixed;
+    {
+        static const char* cap_env = getenv("DPSVM_SP_RES_KB");      // tuning aid: cap the on-chip part
+        if (cap_env && *cap_env) { const size_t cap = (size_t)atoi(cap_env) * 1024; if (cap < res_bytes) res_bytes = cap; }
+    }
+    const size_t per_cta_chunks = ((size_t)a.sp.total_steps / kSpChunk + s_grid - 1) / s_grid + 64;    // no CTA holds more
+    a.sp.res_chunks = (unsigned int)std::min(res_bytes / 1536, per_cta_chunks);
+    const size_t smem = fixed + (size_t)a.sp.res_chunks * 1536;
     a.res_units = 0;
     a.pin_units = 0;
     const bool hint = (variant & 2) != 0;

@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) sparse_count_kernel(const float* __restri
     if (lane == 0 && mine) atomicAdd(total, mine);
 }
 
-// ---- steps per unit: the longest row of the unit over G lanes, rounded up to kSpStepAlign ----------
+// ---- steps per unit: the longest row of the unit over G lanes, in whole chunks (at least one) ----------
 __global__ void __launch_bounds__(256) sparse_unit_steps_kernel(const int* __restrict__ row_nnz, int n, int lanes,
                                                                 unsigned int* __restrict__ unit_steps, int n_units)
 {
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) sparse_unit_steps_kernel(const int* __res
             if (row < n) m = max(m, row_nnz[row]);
         }
         const int steps = (m + lanes - 1) / lanes;
-        unit_steps[u] = (unsigned int)((steps + kSpStepAlign - 1) / kSpStepAlign * kSpStepAlign);
+        unit_steps[u] = (unsigned int)(max(1, (steps + kSpChunk - 1) / kSpChunk) * kSpChunk);
     }
 }
 
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(1024, 1) sparse_scan_kernel(const unsigned int
 // ---- fill: warp per row, ascending columns, entry e -> lane e % G of the row's group, step e / G -----
 __global__ void __launch_bounds__(256) sparse_fill_kernel(const float* __restrict__ x, int n, int pitch, int lanes,
                                                           const unsigned int* __restrict__ unit_off,
-                                                          float* __restrict__ val, unsigned short* __restrict__ col_half)
+                                                          float* __restrict__ val, unsigned short* __restrict__ col)
 {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -113,16 +113,17 @@ __global__ void __launch_bounds__(256) sparse_fill_kernel(const float* __restric
         const unsigned int s0 = unit_off[unit];
         int base = 0;
         for (int c0 = 0; c0 < pitch; c0 += 32) {
-            const int col = c0 + lane;
-            const float v = (col < pitch) ? __ldg(rp + col) : 0.f;
+            const int c = c0 + lane;
+            const float v = (c < pitch) ? __ldg(rp + c) : 0.f;
             const bool nz = v != 0.f;
             const unsigned int mask = __ballot_sync(0xffffffffu, nz);
             if (nz) {
                 const int e = base + __popc(mask & ((1u << lane) - 1u));
                 const unsigned int step = s0 + (unsigned int)(e / lanes);
                 const int slot = grp * lanes + (e % lanes);
-                val[(size_t)step * 32 + slot] = v;
-                col_half[((size_t)(step >> 1) * 32 + slot) * 2 + (step & 1u)] = (unsigned short)(col * 8);
+                const size_t at = ((size_t)(step / kSpChunk) * 32 + slot) * kSpChunk + (step % kSpChunk);   // [chunk][lane][8]
+                val[at] = v;
+                col[at] = (unsigned short)(c * 8);
             }
             base += __popc(mask);
         }
@@ -197,10 +198,10 @@ cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsi
 }
 
 cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
-                               float* val, unsigned int* col2, cudaStream_t s)
+                               float* val, unsigned short* col, cudaStream_t s)
 {
     if (n <= 0) return cudaSuccess;
-    sparse_fill_kernel<<<warp_blocks(n), 256, 0, s>>>(x, n, pitch, lanes, unit_off, val, reinterpret_cast<unsigned short*>(col2));
+    sparse_fill_kernel<<<warp_blocks(n), 256, 0, s>>>(x, n, pitch, lanes, unit_off, val, col);
     return cudaGetLastError();
 }
 
@@ -223,8 +224,8 @@ cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes,
 // ------------------------------------------------------------------------------------------------
 void sparse_release(dpsvm_ctx* c)
 {
-    cudaFree(c->d_sp_val); cudaFree(c->d_sp_col2); cudaFree(c->d_sp_unit_off); cudaFree(c->d_sp_cta_first);
-    c->d_sp_val = nullptr; c->d_sp_col2 = nullptr; c->d_sp_unit_off = nullptr; c->d_sp_cta_first = nullptr;
+    cudaFree(c->d_sp_val); cudaFree(c->d_sp_col); cudaFree(c->d_sp_unit_off); cudaFree(c->d_sp_cta_first);
+    c->d_sp_val = nullptr; c->d_sp_col = nullptr; c->d_sp_unit_off = nullptr; c->d_sp_cta_first = nullptr;
     c->sp = SparseDev{};
     c->sp_nnz = -1;
 }
@@ -311,10 +312,10 @@ int sparse_setup(dpsvm_ctx* c)
     const size_t val_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(float));
     const size_t col_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(unsigned short));
     CU(cudaMalloc(&c->d_sp_val, val_bytes));
-    CU(cudaMalloc(&c->d_sp_col2, col_bytes));
+    CU(cudaMalloc(&c->d_sp_col, col_bytes));
     CU(cudaMemsetAsync(c->d_sp_val, 0, val_bytes, s));
-    CU(cudaMemsetAsync(c->d_sp_col2, 0, col_bytes, s));
-    CU(launch_sparse_fill(x_own, n, pitch, lanes, c->d_sp_unit_off, c->d_sp_val, c->d_sp_col2, s));
+    CU(cudaMemsetAsync(c->d_sp_col, 0, col_bytes, s));
+    CU(launch_sparse_fill(x_own, n, pitch, lanes, c->d_sp_unit_off, c->d_sp_val, c->d_sp_col, s));
     // resident loop: contiguous unit ranges per CTA, balanced by steps (rows differ in length)
     const int grid = resident_grid();
     std::vector<int> first((size_t)grid + 1);
@@ -336,7 +337,7 @@ int sparse_setup(dpsvm_ctx* c)
     CU(launch_sparse_row_norms(c->d_x, c->res_n, pitch, lanes, c->d_xsq, s));
     CU(cudaStreamSynchronize(s));       // `first` is pageable and goes out of scope
     SparseDev sp{};
-    sp.val = c->d_sp_val; sp.col2 = c->d_sp_col2; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
+    sp.val = c->d_sp_val; sp.col = c->d_sp_col; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
     sp.lanes = lanes; sp.n_units = n_units; sp.grid = grid; sp.max_cta_units = max_units;
     sp.total_steps = total_steps; sp.pin_steps = 0;
     c->sp = sp;
