@@ -42,6 +42,10 @@ struct dpsvm_ctx {
     unsigned short* d_sp_col = nullptr;
     unsigned int* d_sp_unit_off = nullptr;
     int* d_sp_cta_first = nullptr;
+    int* d_sp_row_nnz = nullptr;             // build scratch, kept for the next upload
+    unsigned int* d_sp_unit_steps = nullptr;
+    unsigned long long* d_sp_total = nullptr;
+    size_t sp_val_cap = 0, sp_col_cap = 0, sp_units_cap = 0;   // bytes allocated (buffers only grow)
     long long sp_nnz = -1;       // non-zeros of the owned rows (-1: not counted, dense layout forced)
 
     // resident loop (smo_resident.cu)

@@ -222,15 +222,33 @@ cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes,
 // ------------------------------------------------------------------------------------------------
 // Per-context setup: decide the layout, build the stream, compute the row norms in the matching order.
 // ------------------------------------------------------------------------------------------------
+// The stream's buffers live as long as the context and only ever grow: a re-upload (same shape, new data) must not
+// pay for cudaFree / cudaMalloc of a hundred megabytes.
 void sparse_release(dpsvm_ctx* c)
 {
     cudaFree(c->d_sp_val); cudaFree(c->d_sp_col); cudaFree(c->d_sp_unit_off); cudaFree(c->d_sp_cta_first);
+    cudaFree(c->d_sp_row_nnz); cudaFree(c->d_sp_unit_steps); cudaFree(c->d_sp_total);
     c->d_sp_val = nullptr; c->d_sp_col = nullptr; c->d_sp_unit_off = nullptr; c->d_sp_cta_first = nullptr;
+    c->d_sp_row_nnz = nullptr; c->d_sp_unit_steps = nullptr; c->d_sp_total = nullptr;
+    c->sp_val_cap = c->sp_col_cap = c->sp_units_cap = 0;
     c->sp = SparseDev{};
     c->sp_nnz = -1;
 }
 
+template <class T>
+static cudaError_t grow(T*& p, size_t& cap, size_t need)
+{
+    if (p && cap >= need) return cudaSuccess;
+    cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, need);
+    if (e == cudaSuccess) cap = need;
+    return e;
+}
+
 constexpr double kSparseAutoRatio = 0.7;
+constexpr double kSparseMinDenseBytes = 32e6;
 
 static int lanes_for(double mean_nnz)
 {
@@ -257,34 +275,32 @@ static int layout_mode(const dpsvm_ctx* c)
 
 int sparse_setup(dpsvm_ctx* c)
 {
-    sparse_release(c);
+    c->sp = SparseDev{};
+    c->sp_nnz = -1;
     const int mode = layout_mode(c);
     const int n = c->p.shard_rows, pitch = c->pitch;
     const int off = c->p.shard_start - c->res0;
     const float* x_own = c->d_x + (size_t)off * pitch;
     cudaStream_t s = c->stream;
-    if (mode == 1 || pitch > kSparseMaxPitch) {
+    // auto, small shard: dense rows that fit in the SMs' shared memory (or nearly) never leave the chip in the
+    // resident loop and the iteration is bound by its dependency chain, not by bytes -- measured on Adult
+    // 32 561 x 123 (16 MB): 0.274 s to converge dense, 0.291 s sparse.  Not worth counting non-zeros for.
+    const bool small = 4.0 * (double)n * (double)pitch <= kSparseMinDenseBytes;
+    if (mode == 1 || pitch > kSparseMaxPitch || (mode == 0 && small)) {
         if (mode == 2) return fail(DPSVM_ERR_LIMIT, "sparse layout supports rows of at most %d floats (pitch %d)", kSparseMaxPitch, pitch);
         CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
         return DPSVM_OK;
     }
-    int* d_row_nnz = nullptr;
-    unsigned int* d_unit_steps = nullptr;
-    unsigned long long* d_total = nullptr;
-    struct Temps {
-        int*& a; unsigned int*& b; unsigned long long*& t;
-        ~Temps() { cudaFree(a); cudaFree(b); cudaFree(t); }
-    } temps{d_row_nnz, d_unit_steps, d_total};
-    CU(cudaMalloc(&d_row_nnz, sizeof(int) * (size_t)n));
-    CU(cudaMalloc(&d_total, sizeof(unsigned long long)));
-    CU(launch_sparse_count(x_own, n, pitch, d_row_nnz, d_total, s));
+    if (!c->d_sp_row_nnz) CU(cudaMalloc(&c->d_sp_row_nnz, sizeof(int) * (size_t)n));
+    if (!c->d_sp_total) CU(cudaMalloc(&c->d_sp_total, sizeof(unsigned long long)));
+    CU(launch_sparse_count(x_own, n, pitch, c->d_sp_row_nnz, c->d_sp_total, s));
     unsigned long long total = 0;
-    CU(cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(&total, c->d_sp_total, sizeof(total), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     c->sp_nnz = (long long)total;
     const double dense_bytes = 4.0 * (double)n * (double)c->p.num_attributes;
     // auto: sparse when the stream is clearly the smaller one (6 B per non-zero plus padding against 4 B per cell).
-    // Measured at 60 000 x 784 with 38.7 % non-zeros: stream 117 MB vs 188 MB of dense rows, 27.2 vs 33.1 us per
+    // Measured at 60 000 x 784 with 38.7 % non-zeros: stream 123 MB vs 188 MB of dense rows, 25.7 vs 32.7 us per
     // iteration; the sparse sweep sustains about three quarters of the dense sweep's byte rate, so the break-even
     // is near 0.75 and the threshold sits a little below it.
     if (mode == 0 && 6.0 * (double)total > kSparseAutoRatio * dense_bytes) {
@@ -294,25 +310,29 @@ int sparse_setup(dpsvm_ctx* c)
     const int lanes = lanes_for((double)total / (double)n);
     const int groups = 32 / lanes;
     const int n_units = (n + groups - 1) / groups;
-    CU(cudaMalloc(&d_unit_steps, sizeof(unsigned int) * (size_t)n_units));
-    CU(cudaMalloc(&c->d_sp_unit_off, sizeof(unsigned int) * ((size_t)n_units + 1)));
-    CU(launch_sparse_unit_steps(d_row_nnz, n, lanes, d_unit_steps, n_units, s));
-    CU(launch_sparse_scan(d_unit_steps, n_units, c->d_sp_unit_off, s));
+    {
+        // unit_steps and unit_off are sized for the finest units (4 lanes per row would give the fewest; 32 the most)
+        const size_t need = sizeof(unsigned int) * ((size_t)n + 1);
+        size_t cap_a = c->sp_units_cap, cap_b = c->sp_units_cap;
+        CU(grow(c->d_sp_unit_steps, cap_a, need));
+        CU(grow(c->d_sp_unit_off, cap_b, need));
+        c->sp_units_cap = need;
+    }
+    CU(launch_sparse_unit_steps(c->d_sp_row_nnz, n, lanes, c->d_sp_unit_steps, n_units, s));
+    CU(launch_sparse_scan(c->d_sp_unit_steps, n_units, c->d_sp_unit_off, s));
     std::vector<unsigned int> h_off((size_t)n_units + 1);
     CU(cudaMemcpyAsync(h_off.data(), c->d_sp_unit_off, sizeof(unsigned int) * h_off.size(), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     const unsigned int total_steps = h_off[n_units];
     const double stream_bytes = 192.0 * (double)total_steps;
     if (mode == 0 && stream_bytes > kSparseAutoRatio * dense_bytes) {
-        sparse_release(c);
-        c->sp_nnz = (long long)total;
         CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
         return DPSVM_OK;
     }
     const size_t val_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(float));
     const size_t col_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(unsigned short));
-    CU(cudaMalloc(&c->d_sp_val, val_bytes));
-    CU(cudaMalloc(&c->d_sp_col, col_bytes));
+    CU(grow(c->d_sp_val, c->sp_val_cap, val_bytes));
+    CU(grow(c->d_sp_col, c->sp_col_cap, col_bytes));
     CU(cudaMemsetAsync(c->d_sp_val, 0, val_bytes, s));
     CU(cudaMemsetAsync(c->d_sp_col, 0, col_bytes, s));
     CU(launch_sparse_fill(x_own, n, pitch, lanes, c->d_sp_unit_off, c->d_sp_val, c->d_sp_col, s));
@@ -332,14 +352,15 @@ int sparse_setup(dpsvm_ctx* c)
         if (first[i + 1] < first[i]) first[i + 1] = first[i];
         max_units = std::max(max_units, first[i + 1] - first[i]);
     }
-    CU(cudaMalloc(&c->d_sp_cta_first, sizeof(int) * first.size()));
+    if (!c->d_sp_cta_first) CU(cudaMalloc(&c->d_sp_cta_first, sizeof(int) * 1025));
+    if (grid > 1024) return fail(DPSVM_ERR_LIMIT, "resident grid of %d CTAs", grid);
     CU(cudaMemcpyAsync(c->d_sp_cta_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice, s));
     CU(launch_sparse_row_norms(c->d_x, c->res_n, pitch, lanes, c->d_xsq, s));
     CU(cudaStreamSynchronize(s));       // `first` is pageable and goes out of scope
     SparseDev sp{};
     sp.val = c->d_sp_val; sp.col = c->d_sp_col; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
     sp.lanes = lanes; sp.n_units = n_units; sp.grid = grid; sp.max_cta_units = max_units;
-    sp.total_steps = total_steps; sp.pin_steps = 0;
+    sp.total_steps = total_steps; sp.pin_steps = 0; sp.res_chunks = 0;
     c->sp = sp;
     return DPSVM_OK;
 }

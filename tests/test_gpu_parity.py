@@ -566,23 +566,35 @@ def _device_floats(ptr, n):
     return out
 
 
-def test_layout_is_chosen_from_the_share_of_nonzeros(golden, monkeypatch):
+def test_layout_is_chosen_from_size_and_share_of_nonzeros(golden, monkeypatch):
     monkeypatch.delenv("DPSVM_LAYOUT", raising=False)
     monkeypatch.delenv("DPSVM_SPARSE_LANES", raising=False)
-    g = golden("adult_2048")                      # 14 ones in 123 columns
+    g = golden("adult_2048")                      # 14 ones in 123 columns, but a shard this small stays dense
     with _trainer(g) as t:
+        assert t.layout_info() == (0, -1, int(g["n"]) * capi.pitch_for(int(g["d"])) * 4)
+    with _trainer(g, flags=capi.FLAG_SPARSE) as t:
         lanes, nnz, sweep = t.layout_info()
         assert lanes == 4 and nnz == int(np.count_nonzero(g["x"])) and sweep < 0.5 * g["x"].nbytes
-    with _trainer(g, flags=capi.FLAG_DENSE) as t:
-        assert t.layout_info()[0] == 0 and t.layout_info()[2] == int(g["n"]) * capi.pitch_for(int(g["d"])) * 4
     g = golden("mnist_512")                       # 39 % non-zero
-    with _trainer(g) as t:
-        assert t.layout_info()[0] == 8 and t.layout_info()[1] == int(np.count_nonzero(g["x"]))
-    g = golden("odd_d_333x37")                    # no zeros at all: dense unless forced
-    with _trainer(g) as t:
-        assert t.layout_info()[0] == 0
     with _trainer(g, flags=capi.FLAG_SPARSE) as t:
-        assert t.layout_info()[0] in (4, 8) and t.layout_info()[1] == int(np.count_nonzero(g["x"]))
+        assert t.layout_info()[0] == 8 and t.layout_info()[1] == int(np.count_nonzero(g["x"]))
+    with _trainer(g, flags=capi.FLAG_DENSE) as t:
+        assert t.layout_info()[0] == 0
+    # shards beyond what the SMs can hold: sparse when the stream is clearly smaller than the dense rows
+    rng = np.random.default_rng(3)
+    n, d = 48000, 256
+    x = (rng.random((n, d), dtype=np.float32) < 0.2).astype(np.float32) * rng.random((n, d), dtype=np.float32)
+    y = np.where(rng.random(n) < 0.5, 1, -1).astype(np.int32)
+    with capi.Trainer(n, d, 1.0, 0.05, 1e-3, cache_size=0) as t:
+        t.upload(x, y)
+        lanes, nnz, sweep = t.layout_info()
+        assert lanes == 8 and nnz == int(np.count_nonzero(x)) and sweep < 0.5 * x.nbytes
+        t.upload(np.ascontiguousarray(rng.random((n, d), dtype=np.float32)), y)      # same context, no zeros: back to dense
+        assert t.layout_info()[0] == 0 and t.layout_info()[1] == n * d
+        assert t.train(5).num_iter == 5
+        t.upload(x, y)                                                              # and sparse again (buffers are reused)
+        assert t.layout_info()[0] == 8
+        assert t.train(5).num_iter == 5
     # rows wider than the sparse sweep supports: auto falls back to dense, forcing sparse is an error
     x = np.zeros((8, 1100), np.float32)
     x[:, 3] = 1.0
