@@ -33,7 +33,7 @@ struct PushDev;
 // context are summed in the same order (sparse_row_norms), so <x_i,x_i> == |x_i|^2 stays bit-exact.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpChunk = 8;             // steps per chunk = alignment of a unit's step count
-constexpr int kSpRing = 2;              // register chunks per warp: one being consumed, one in flight
+constexpr int kSpRing = 4;              // register chunks per warp: one being consumed, three in flight (what an HBM-sized stream needs)
 struct SparseDev {
     const float* val;           // null: dense sweep
     const unsigned short* col;
