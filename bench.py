@@ -390,6 +390,8 @@ def main():
                      "algorithmic_bytes_basis": ("sparse stream: 6 B per non-zero + 20 B per row (+ 8 B per row of cache-line stores)" if lanes
                                                  else "SURVEY 8(d): 4 n d + 20 n (+ 8 n of cache-line stores)"),
                      "dense_rows_equivalent_GBps": dense_abytes / (iter_ms * 1e-3) / 1e9,
+                     "note": ("the sparse sweep is limited by its shared-memory gathers (LSU), and a stream of up to ~120 MB is served from L2 "
+                              "and shared memory, not HBM (profiles/r01_sparse_ncu_summary.md); frac is still quoted against the HBM copy peak") if lanes else None,
                      "kernel_us": 1e3 * kernel_ms, "timing": timing, "share_of_step": share},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(4 * n_shard * d + 4 * n_shard),
                 "d2h_bytes_per_step": int(4 * n_shard + 64), "iters_per_step": e2e_iters,
