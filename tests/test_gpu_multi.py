@@ -26,9 +26,10 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, name, cache, exchange, out_dir):
+def _worker(rank, world, port, name, cache, exchange, out_dir, layout="auto"):
     graph_loop = exchange.endswith("+graph")
     exchange = exchange.split("+")[0]
+    os.environ["DPSVM_LAYOUT"] = layout
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
@@ -60,14 +61,18 @@ def _worker(rank, world, port, name, cache, exchange, out_dir):
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("name,cache,exchange", [("mnist_512", 0, "p2p"), ("adult_2048", 10, "p2p"), ("odd_d_333x37", 4, "p2p"),
-                                                 ("mnist_512", 10, "p2p+graph"), ("adult_2048", 0, "p2p+graph"),
-                                                 ("mnist_512", 10, "nccl"), ("odd_d_333x37", 0, "nccl")])
-def test_sharded_training_equals_single_gpu(golden, tmp_path, name, cache, exchange):
+@pytest.mark.parametrize("name,cache,exchange,layout", [
+    ("mnist_512", 0, "p2p", "auto"), ("adult_2048", 10, "p2p", "auto"), ("odd_d_333x37", 4, "p2p", "auto"),
+    ("mnist_512", 10, "p2p+graph", "auto"), ("adult_2048", 0, "p2p+graph", "auto"),
+    ("mnist_512", 10, "nccl", "auto"), ("odd_d_333x37", 0, "nccl", "auto"),
+    # the same exchanges with every rank sweeping the sparse stream of its shard (goldens are small: auto keeps them dense)
+    ("mnist_512", 10, "p2p", "sparse"), ("adult_2048", 0, "p2p+graph", "sparse"), ("mnist_512", 0, "nccl", "sparse")])
+def test_sharded_training_equals_single_gpu(golden, tmp_path, monkeypatch, name, cache, exchange, layout):
     import torch.multiprocessing as mp
     from dpsvm_b200 import capi
+    monkeypatch.setenv("DPSVM_LAYOUT", layout)
     world = min(_ngpu(), 4 if name == "adult_2048" else 2)
-    mp.spawn(_worker, args=(world, _free_port(), name, cache, exchange, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), name, cache, exchange, str(tmp_path), layout), nprocs=world, join=True)
     g = golden(name)
     with capi.Trainer(int(g["n"]), int(g["d"]), float(g["c"]), float(g["gamma"]), float(g["epsilon"]),
                       max_iter=int(g["max_iter"]), cache_size=cache) as t:
