@@ -286,7 +286,11 @@ int sparse_setup(dpsvm_ctx* c)
     // resident loop and the iteration is bound by its dependency chain, not by bytes -- measured on Adult
     // 32 561 x 123 (16 MB): 0.274 s to converge dense, 0.291 s sparse.  Not worth counting non-zeros for.
     const bool small = 4.0 * (double)n * (double)pitch <= kSparseMinDenseBytes;
-    if (mode == 1 || pitch > kSparseMaxPitch || (mode == 0 && small)) {
+    // auto, drop-in layout with the whole of X on every rank (svmTrain.cu:344) but only a shard owned: |x|^2 of the
+    // rows other ranks own would be summed in THIS rank's order, which need not be the owner's (the lane count
+    // follows the shard's mean row length).  Keep the one order every rank shares.
+    const bool foreign_rows = c->res_n != n;
+    if (mode == 1 || pitch > kSparseMaxPitch || (mode == 0 && (small || foreign_rows))) {
         if (mode == 2) return fail(DPSVM_ERR_LIMIT, "sparse layout supports rows of at most %d floats (pitch %d)", kSparseMaxPitch, pitch);
         CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
         return DPSVM_OK;
