@@ -45,6 +45,15 @@ __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_sr
 }
 
 __device__ __forceinline__ unsigned long long umin64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
+// Warp-wide minimum of 64-bit keys in two redux.sync: the high words, then the low words of the lanes that hold the
+// minimal high word.  Every lane gets the result.
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long k)
+{
+    const unsigned int hi = (unsigned int)(k >> 32), lo = (unsigned int)k;
+    const unsigned int min_hi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned int min_lo = __reduce_min_sync(0xffffffffu, hi == min_hi ? lo : 0xffffffffu);
+    return ((unsigned long long)min_hi << 32) | min_lo;
+}
 
 __device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v)
 {

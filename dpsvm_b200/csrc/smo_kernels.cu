@@ -41,21 +41,13 @@ __device__ __forceinline__ void publish_keys(unsigned long long best_up, unsigne
                                              unsigned long long* keys, unsigned long long* s_red)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        best_up = umin64(best_up, __shfl_xor_sync(0xffffffffu, best_up, off));
-        best_low = umin64(best_low, __shfl_xor_sync(0xffffffffu, best_low, off));
-    }
+    best_up = warp_min_u64(best_up);
+    best_low = warp_min_u64(best_low);
     if (lane == 0) { s_red[warp] = best_up; s_red[nwarps + warp] = best_low; }
     __syncthreads();
     if (warp == 0) {
-        unsigned long long u = lane < nwarps ? s_red[lane] : DPSVM_KEY_EMPTY;
-        unsigned long long l = lane < nwarps ? s_red[nwarps + lane] : DPSVM_KEY_EMPTY;
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-            u = umin64(u, __shfl_xor_sync(0xffffffffu, u, off));
-            l = umin64(l, __shfl_xor_sync(0xffffffffu, l, off));
-        }
+        const unsigned long long u = warp_min_u64(lane < nwarps ? s_red[lane] : DPSVM_KEY_EMPTY);
+        const unsigned long long l = warp_min_u64(lane < nwarps ? s_red[nwarps + lane] : DPSVM_KEY_EMPTY);
         if (lane == 0) {
             if (u != DPSVM_KEY_EMPTY) atomicMin(&keys[0], u);
             if (l != DPSVM_KEY_EMPTY) atomicMin(&keys[1], l);

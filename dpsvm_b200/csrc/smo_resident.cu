@@ -78,14 +78,18 @@ __device__ __forceinline__ void cand_min(Cand& a, unsigned long long k, float al
 {
     if (k < a.key) { a.key = k; a.alpha = al; }
 }
+// Warp-wide minimum of the packed keys, with the alpha that belongs to the winner; every lane ends up with the
+// result.  Two redux.sync (high word, then low word among the lanes that hold the minimal high word), a ballot and
+// one shuffle instead of five butterfly levels of three shuffles each: this sits on the per-iteration dependency
+// chain four times (block best and grid best, two stages each).
 __device__ __forceinline__ void cand_warp_min(Cand& a)
 {
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const unsigned long long k = __shfl_xor_sync(0xffffffffu, a.key, off);
-        const float al = __shfl_xor_sync(0xffffffffu, a.alpha, off);
-        cand_min(a, k, al);
-    }
+    const unsigned int hi = (unsigned int)(a.key >> 32), lo = (unsigned int)a.key;
+    const unsigned int min_hi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned int min_lo = __reduce_min_sync(0xffffffffu, hi == min_hi ? lo : 0xffffffffu);
+    const unsigned int who = __ballot_sync(0xffffffffu, hi == min_hi && lo == min_lo);     // never empty
+    a.alpha = __shfl_sync(0xffffffffu, a.alpha, __ffs((int)who) - 1);
+    a.key = ((unsigned long long)min_hi << 32) | min_lo;
 }
 
 // Exact LRU over a small table, replicated in every CTA (cache.cu:62-105 semantics: a lookup hit
@@ -152,8 +156,6 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     __shared__ int s_flag;
     __shared__ int s_lru_key[kResCacheLines], s_lru_stamp[kResCacheLines], s_lru_meta[2];
     __shared__ PassScalars s_ps;
-    __shared__ float s_next[8];                        // merged pair for the next iteration
-    __shared__ unsigned long long s_next_key[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sub = SPARSE ? lane % SGL : lane % LPR, grp = SPARSE ? lane / SGL : lane / LPR;
@@ -559,6 +561,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         stamp(it, 3);
 
         // every CTA merges all slots: minimum packed key = lowest global index among equal f
+        Cand nxt_up, nxt_low;
         {
             Cand u{DPSVM_KEY_EMPTY, 0.f}, l{DPSVM_KEY_EMPTY, 0.f};
             for (int c = tid; c < G; c += kResThreads) {
@@ -571,25 +574,22 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             cand_warp_min(l);
             if (lane == 0) { s_cand[0][warp] = u; s_cand[1][warp] = l; }
             __syncthreads();
-            if (warp == 0) {
-                Cand uu = lane < NW ? s_cand[0][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
-                Cand ll = lane < NW ? s_cand[1][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
-                cand_warp_min(uu);
-                cand_warp_min(ll);
-                if (lane == 0) { s_next_key[0] = uu.key; s_next_key[1] = ll.key; s_next[0] = uu.alpha; s_next[1] = ll.alpha; }
-            }
-            __syncthreads();
+            // every warp finishes the reduction for itself: no second barrier, no broadcast through shared memory
+            nxt_up = lane < NW ? s_cand[0][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
+            nxt_low = lane < NW ? s_cand[1][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
+            cand_warp_min(nxt_up);
+            cand_warp_min(nxt_low);
         }
         // multi-GPU: CTA 0 publishes this rank's candidates to every rank (also on the last iteration of the
         // launch: the next launch starts by waiting for exactly these packages)
         stamp(it, 4);
-        if (a.world > 1 && cta == 0) push_package(*a.push, s_next_key[0], s_next_key[1], s_next[0], s_next[1], true, (unsigned int)num_iter);
+        if (a.world > 1 && cta == 0) push_package(*a.push, nxt_up.key, nxt_low.key, nxt_up.alpha, nxt_low.alpha, true, (unsigned int)num_iter);
         stamp(it, 5);
         if (last_iter) {
             if (cta == 0 && tid == 0) {
-                a.keys[0] = s_next_key[0];
-                a.keys[1] = s_next_key[1];
-                if (a.world > 1) { a.push->keys_copy[0] = s_next_key[0]; a.push->keys_copy[1] = s_next_key[1]; }
+                a.keys[0] = nxt_up.key;
+                a.keys[1] = nxt_low.key;
+                if (a.world > 1) { a.push->keys_copy[0] = nxt_up.key; a.push->keys_copy[1] = nxt_low.key; }
                 if (!keep_going) { st->converged = 1; st->done = 1; }
                 if (num_iter >= a.max_iter) st->done = 1;
             }
@@ -599,12 +599,12 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             if (!acquire_remote((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
             stamp(it, 6);
         } else {
-            unpack_key_up(s_next_key[0], &b_hi, &i_hi);
-            unpack_key_low(s_next_key[1], &b_lo, &i_lo);
-            a_hi_old = s_next[0];
-            a_lo_old = s_next[1];
+            unpack_key_up(nxt_up.key, &b_hi, &i_hi);
+            unpack_key_low(nxt_low.key, &b_lo, &i_lo);
+            a_hi_old = nxt_up.alpha;
+            a_lo_old = nxt_low.alpha;
         }
-        __syncthreads();        // s_next / s_cand are rewritten next round
+        // (s_cand is next written after a whole sweep, with several block barriers in between)
     }
     if (cta == 0 && a.cache_lines > 0) {
         __syncthreads();
