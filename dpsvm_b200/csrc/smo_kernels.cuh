@@ -30,7 +30,8 @@ struct PushDev;
 //
 // Dot-product order of the sparse layout (the counterpart of DotGeom): per lane sequential FMAs over
 // its entries in step order, then an xor-butterfly over the G lanes.  The row norms of a sparse
-// context are summed in the same order (sparse_row_norms), so <x_i,x_i> == |x_i|^2 stays bit-exact.
+// context are summed from the stream in the same order (sparse_row_norms_kernel), so <x_i,x_i> == |x_i|^2
+// stays bit-exact.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpChunk = 8;             // steps per chunk = alignment of a unit's step count
 constexpr int kSpRing = 4;              // register chunks per warp: one being consumed, three in flight (what an HBM-sized stream needs)
@@ -232,6 +233,6 @@ cudaError_t launch_sparse_unit_steps(const int* row_nnz, int n, int lanes, unsig
 cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsigned int* unit_off, cudaStream_t s);
 cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
                                float* val, unsigned short* col, cudaStream_t s);
-cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes, float* out, cudaStream_t s);
+cudaError_t launch_sparse_row_norms(const float* val, const unsigned int* unit_off, int n_units, int n, int lanes, float* out, cudaStream_t s);
 
 }  // namespace dpsvm

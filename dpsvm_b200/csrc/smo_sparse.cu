@@ -130,38 +130,30 @@ __global__ void __launch_bounds__(256) sparse_fill_kernel(const float* __restric
     }
 }
 
-// ---- |x_i|^2 in the sparse sweep's order, straight from the dense row ---------------------------------
-// Lane g < G plays the sweep's lane g: it squares the non-zeros e = g, g + G, ... in ascending order with
-// sequential FMAs; then the same xor-butterfly over the G lanes.
+// ---- |x_i|^2 in the sparse sweep's order, from the stream itself ---------------------------------------
+// A warp per unit, every lane walks its own entries exactly as the sweep does (sequential FMAs in step order, the
+// value taking the place of both operands), then the same xor-butterfly over the G lanes of a row.
 template <int G>
-__global__ void __launch_bounds__(256) sparse_row_norms_kernel(const float* __restrict__ x, int n, int pitch, float* __restrict__ out)
+__global__ void __launch_bounds__(256) sparse_row_norms_kernel(const float* __restrict__ val, const unsigned int* __restrict__ unit_off,
+                                                               int n_units, int n, float* __restrict__ out)
 {
+    constexpr int GROUPS = 32 / G;
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int n_warps = (gridDim.x * blockDim.x) >> 5;
-    for (int row = warp; row < n; row += n_warps) {
-        const float* rp = x + (size_t)row * pitch;
+    for (int u = warp; u < n_units; u += n_warps) {
+        const unsigned int c0 = unit_off[u] / kSpChunk, c1 = unit_off[u + 1] / kSpChunk;
         float acc = 0.f;
-        int base = 0;
-        for (int c0 = 0; c0 < pitch; c0 += 32) {
-            const float v = (c0 + lane < pitch) ? __ldg(rp + c0 + lane) : 0.f;
-            const unsigned int mask = __ballot_sync(0xffffffffu, v != 0.f);
-            const int cnt = __popc(mask);
-            const int j0 = (lane - base) & (G - 1);        // first entry of this chunk that belongs to lane g
-#pragma unroll
-            for (int r = 0; r < 32 / G; ++r) {
-                const int j = j0 + r * G;
-                const bool ok = lane < G && j < cnt;
-                const unsigned int src = ok ? __fns(mask, 0, j + 1) : 0u;
-                const float w = __shfl_sync(0xffffffffu, v, (int)(src & 31u));
-                if (ok) acc = __fmaf_rn(w, w, acc);
-            }
-            base += cnt;
+        for (unsigned int q = c0; q < c1; ++q) {
+            const float4* vp = reinterpret_cast<const float4*>(val + ((size_t)q * 32 + lane) * kSpChunk);
+            const float4 a = __ldg(vp), b = __ldg(vp + 1);
+            acc = __fmaf_rn(a.x, a.x, acc); acc = __fmaf_rn(a.y, a.y, acc); acc = __fmaf_rn(a.z, a.z, acc); acc = __fmaf_rn(a.w, a.w, acc);
+            acc = __fmaf_rn(b.x, b.x, acc); acc = __fmaf_rn(b.y, b.y, acc); acc = __fmaf_rn(b.z, b.z, acc); acc = __fmaf_rn(b.w, b.w, acc);
         }
-        if (lane >= G) acc = 0.f;
 #pragma unroll
         for (int off = G / 2; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
-        if (lane == 0) out[row] = acc;
+        const int row = u * GROUPS + lane / G;
+        if (lane % G == 0 && row < n) out[row] = acc;
     }
 }
 
@@ -205,15 +197,15 @@ cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, cons
     return cudaGetLastError();
 }
 
-cudaError_t launch_sparse_row_norms(const float* x, int n, int pitch, int lanes, float* out, cudaStream_t s)
+cudaError_t launch_sparse_row_norms(const float* val, const unsigned int* unit_off, int n_units, int n, int lanes, float* out, cudaStream_t s)
 {
-    if (n <= 0) return cudaSuccess;
-    const int blocks = warp_blocks(n);
+    if (n_units <= 0) return cudaSuccess;
+    const int blocks = warp_blocks(n_units);
     switch (lanes) {
-        case 4: sparse_row_norms_kernel<4><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
-        case 8: sparse_row_norms_kernel<8><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
-        case 16: sparse_row_norms_kernel<16><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
-        case 32: sparse_row_norms_kernel<32><<<blocks, 256, 0, s>>>(x, n, pitch, out); break;
+        case 4: sparse_row_norms_kernel<4><<<blocks, 256, 0, s>>>(val, unit_off, n_units, n, out); break;
+        case 8: sparse_row_norms_kernel<8><<<blocks, 256, 0, s>>>(val, unit_off, n_units, n, out); break;
+        case 16: sparse_row_norms_kernel<16><<<blocks, 256, 0, s>>>(val, unit_off, n_units, n, out); break;
+        case 32: sparse_row_norms_kernel<32><<<blocks, 256, 0, s>>>(val, unit_off, n_units, n, out); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -359,7 +351,10 @@ int sparse_setup(dpsvm_ctx* c)
     if (!c->d_sp_cta_first) CU(cudaMalloc(&c->d_sp_cta_first, sizeof(int) * 1025));
     if (grid > 1024) return fail(DPSVM_ERR_LIMIT, "resident grid of %d CTAs", grid);
     CU(cudaMemcpyAsync(c->d_sp_cta_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice, s));
-    CU(launch_sparse_row_norms(c->d_x, c->res_n, pitch, lanes, c->d_xsq, s));
+    // the owned rows are all the rows this rank holds here (a forced sparse layout with foreign rows resident keeps
+    // the dense-order norms for those: they only ever serve as the partner's |x|^2 in another row's kernel value)
+    if (foreign_rows) CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+    CU(launch_sparse_row_norms(c->d_sp_val, c->d_sp_unit_off, n_units, n, lanes, c->d_xsq + off, s));
     CU(cudaStreamSynchronize(s));       // `first` is pageable and goes out of scope
     SparseDev sp{};
     sp.val = c->d_sp_val; sp.col = c->d_sp_col; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
