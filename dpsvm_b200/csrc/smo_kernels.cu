@@ -801,17 +801,18 @@ static cudaError_t launch_ex(void (*kernel)(KArgs...), int blocks, int threads, 
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
-static int g_num_sms = 0;
+// SM count of the CURRENT device (cached per device; racing first calls store the same value).
 int device_sm_count()
 {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    static int s_sms[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (s_sms[dev] == 0) {
         int v = 0;
         if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return 148;
-        g_num_sms = v;
+        s_sms[dev] = v;
     }
-    return g_num_sms;
+    return s_sms[dev];
 }
 
 template <int LPR, int ITERS>
@@ -881,11 +882,13 @@ cudaError_t launch_pass(const PassDev& a, int variant, cudaStream_t s)
         const int cap4 = ((a.pitch4 + 31) / 32) * 32;
         const size_t smem = (size_t)cap4 * 2 * sizeof(float4);
         if (smem > 200 * 1024) return cudaErrorInvalidValue;
-        static bool attr_set = false;
-        if (!attr_set) {
+        static bool attr_set[64] = {false};      // function attributes belong to the device they were set on
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+        if (!attr_set[dev]) {
             cudaError_t e = cudaFuncSetAttribute(smo_pass_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) return e;
-            attr_set = true;
+            attr_set[dev] = true;
         }
         const int n_units = (a.n + kRowsInFlight - 1) / kRowsInFlight;
         int blocks = (n_units + 7) / 8;

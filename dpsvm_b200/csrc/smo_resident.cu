@@ -30,6 +30,7 @@
 //     mailbox over NVLink; every CTA then waits on the arrival flags and merges the packages itself.
 #include <algorithm>
 #include <limits.h>
+#include <mutex>
 #include <math.h>
 #include <stdlib.h>
 
@@ -616,6 +617,47 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
 // ------------------------------------------------------------------------------------------------
 // launcher
 // ------------------------------------------------------------------------------------------------
+// Per kernel instantiation and per device: the dynamic shared-memory budget (function attributes belong to the
+// device they were set on) and the grid.  Filled once under a lock; host threads may share the library.
+struct ResCfg {
+    int smem_max = -1;
+    int grid = 0;
+};
+constexpr int kMaxDevices = 64;
+
+static cudaError_t resident_config(const void* kernel, int min_budget, ResCfg (&cache)[kMaxDevices], std::mutex& mu, ResCfg* out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    ResCfg& c = cache[dev];
+    if (c.smem_max < 0) {
+        int optin = 0, sms = 0;
+        e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        if (e != cudaSuccess) return e;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        cudaFuncAttributes fa;
+        e = cudaFuncGetAttributes(&fa, kernel);
+        if (e != cudaSuccess) return e;
+        const int budget = optin - (int)fa.sharedSizeBytes - 1024;
+        if (budget < min_budget) return cudaErrorInvalidValue;
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, budget);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kResThreads, budget);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        if (sms < 1 || sms > kResThreads) return cudaErrorInvalidValue;      // thread c of a CTA reads CTA c's slot
+        c.grid = sms;
+        c.smem_max = budget;
+    }
+    *out = c;
+    return cudaSuccess;
+}
+
 constexpr int kResSliceUnits = 16;     // on-chip units per CTA when the shard does not fit on chip entirely
 
 template <int LPR, int ITERS>
@@ -624,27 +666,14 @@ static cudaError_t launch_resident_t(ResidentDev a, int variant, cudaStream_t s)
     constexpr int RPW = (32 / LPR) * kRowsInFlight;
     constexpr int CAP4 = LPR * ITERS;
     auto kernel = smo_resident_kernel<LPR, ITERS, 0>;
-    static int s_smem_max = -1, s_grid = 0;
-    if (s_smem_max < 0) {
-        int dev = 0, optin = 0;
-        cudaError_t e = cudaGetDevice(&dev);
+    static ResCfg s_cache[kMaxDevices];
+    static std::mutex s_mu;
+    ResCfg cfg;
+    {
+        const cudaError_t e = resident_config((const void*)kernel, 2 * CAP4 * 16, s_cache, s_mu, &cfg);
         if (e != cudaSuccess) return e;
-        e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        if (e != cudaSuccess) return e;
-        cudaFuncAttributes fa;
-        e = cudaFuncGetAttributes(&fa, kernel);
-        if (e != cudaSuccess) return e;
-        int budget = optin - (int)fa.sharedSizeBytes - 1024;
-        if (budget < 2 * CAP4 * 16) return cudaErrorInvalidValue;
-        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, budget);
-        if (e != cudaSuccess) return e;
-        int per_sm = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kResThreads, budget);
-        if (e != cudaSuccess) return e;
-        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        s_grid = device_sm_count();
-        s_smem_max = budget;
     }
+    const int s_smem_max = cfg.smem_max, s_grid = cfg.grid;
     const size_t unit_bytes = (size_t)RPW * a.pitch4 * 16;
     const size_t unit_smem = unit_bytes + (size_t)RPW * 16;          // rows + |x|^2, y, f, alpha
     const size_t avail = (size_t)s_smem_max - 2 * (size_t)CAP4 * 16;
@@ -699,26 +728,14 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
     constexpr int CAP4 = 256;
     static_assert(CAP4 * 4 == kSparseMaxPitch, "selected-row buffers cover the widest sparse row");
     auto kernel = smo_resident_kernel<32, 8, SG>;
-    static int s_smem_max = -1, s_grid = 0;
-    if (s_smem_max < 0) {
-        int dev = 0, optin = 0;
-        cudaError_t e = cudaGetDevice(&dev);
+    static ResCfg s_cache[kMaxDevices];
+    static std::mutex s_mu;
+    ResCfg cfg;
+    {
+        const cudaError_t e = resident_config((const void*)kernel, 64 * 1024, s_cache, s_mu, &cfg);
         if (e != cudaSuccess) return e;
-        e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        if (e != cudaSuccess) return e;
-        cudaFuncAttributes fa;
-        e = cudaFuncGetAttributes(&fa, kernel);
-        if (e != cudaSuccess) return e;
-        const int budget = optin - (int)fa.sharedSizeBytes - 1024;
-        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, budget);
-        if (e != cudaSuccess) return e;
-        int per_sm = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kResThreads, 64 * 1024);
-        if (e != cudaSuccess) return e;
-        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        s_grid = device_sm_count();
-        s_smem_max = budget;
     }
+    const int s_smem_max = cfg.smem_max, s_grid = cfg.grid;
     if (a.sp.grid != s_grid) return cudaErrorInvalidValue;      // cta_first was balanced for another grid
     const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int);
     if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;

@@ -87,3 +87,34 @@ def test_sharded_training_equals_single_gpu(golden, tmp_path, monkeypatch, name,
         assert int(p["hits"]) == st.cache_hits
     assert np.array_equal(np.concatenate([p["alpha"] for p in parts]), alpha)
     assert np.array_equal(np.concatenate([p["f"] for p in parts]), f)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("layout", ["dense", "sparse"])
+def test_one_process_two_devices(golden, monkeypatch, layout):
+    """The C ABI takes an explicit device ordinal (the reference never calls cudaSetDevice): two contexts on two
+    GPUs driven by ONE process give the same result (kernel attributes are set per device, not per process)."""
+    from dpsvm_b200 import capi
+    monkeypatch.setenv("DPSVM_LAYOUT", layout)
+    g = golden("mnist_512")
+    out = []
+    for dev in (0, 1, 0):
+        with capi.Trainer(int(g["n"]), int(g["d"]), float(g["c"]), float(g["gamma"]), float(g["epsilon"]),
+                          max_iter=int(g["max_iter"]), cache_size=10, device=dev) as t:
+            t.upload(np.ascontiguousarray(g["x"]), np.ascontiguousarray(g["y"]))
+            st = t.train()
+            alpha, f, _ = t.download()
+            out.append((st.num_iter, alpha, f))
+    for it, alpha, f in out[1:]:
+        assert it == out[0][0] and np.array_equal(alpha, out[0][1]) and np.array_equal(f, out[0][2])
+    # wide rows: the generic pass kernel's shared-memory attribute must be set on the second device too
+    monkeypatch.setenv("DPSVM_LAYOUT", "auto")        # rows of 1100 floats have no sparse sweep
+    rng = np.random.default_rng(1)
+    x = rng.random((64, 1100), dtype=np.float32)
+    y = np.where(rng.random(64) < 0.5, 1, -1).astype(np.int32)
+    its = []
+    for dev in (0, 1):
+        with capi.Trainer(64, 1100, 1.0, 0.01, 1e-3, cache_size=0, device=dev) as t:
+            t.upload(x, y)
+            its.append(t.train(50).num_iter)
+    assert its[0] == its[1] == 50
