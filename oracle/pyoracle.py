@@ -216,5 +216,23 @@ def lru_replay(keys, capacity):
     return hits, hit, line
 
 
+def dot_dense_order(x_row, h) -> np.float32:
+    """<x_row, h> summed in the dense kernels' order (oracle_dot_dense_order)."""
+    x_row, h = np.ascontiguousarray(x_row, np.float32), np.ascontiguousarray(h, np.float32)
+    fn = port().oracle_dot_dense_order
+    fn.restype = C.c_float
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    return np.float32(fn(x_row.ctypes.data, h.ctypes.data, x_row.shape[0]))
+
+
+def dot_sparse_order(x_row, h, lanes) -> np.float32:
+    """<x_row, h> summed in the sparse sweep's order with `lanes` lanes per row (oracle_dot_sparse_order)."""
+    x_row, h = np.ascontiguousarray(x_row, np.float32), np.ascontiguousarray(h, np.float32)
+    fn = port().oracle_dot_sparse_order
+    fn.restype = C.c_float
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    return np.float32(fn(x_row.ctypes.data, h.ctypes.data, x_row.shape[0], lanes))
+
+
 def max_threads() -> int:
     return int(port().oracle_max_threads())

@@ -333,6 +333,64 @@ int oracle_lru_replay(const int* keys, int num, int capacity, unsigned char* hit
     return hits;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * The two dot-product ORDERS of the CUDA path, restated on the CPU so that the kernels can be checked bit
+ * for bit against something that is not themselves (tests/test_gpu_parity.py reads the dot products back
+ * from the kernel-row cache).  These are specifications of this repository, not of the reference, whose
+ * cublasSgemv (svmTrain.cu:222,247) fixes no order; fmaf() is the correctly rounded fused multiply-add.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Dense rows (DotGeom, dpsvm_b200/csrc/smo_common.cuh): the row, zero padded to pitch4 = ceil(d/4) float4
+ * chunks, is split over LPR lanes (4/8/16/32 by pitch4); lane s takes chunks s, s+LPR, ... and adds their
+ * x,y,z,w products with sequential FMAs; an xor-butterfly (offsets LPR/2 .. 1) sums the lanes. */
+float oracle_dot_dense_order(const float* x, const float* h, int d)
+{
+    const int pitch4 = (d + 3) / 4;
+    const int lpr = pitch4 <= 32 ? 4 : pitch4 <= 64 ? 8 : pitch4 <= 128 ? 16 : 32;
+    const int iters = (pitch4 + lpr - 1) / lpr;
+    float acc[32];
+    for (int s = 0; s < lpr; ++s) {
+        float a = 0.0f;
+        for (int it = 0; it < iters; ++it) {
+            const int c4 = s + it * lpr;
+            for (int k = 0; k < 4; ++k) {
+                const int c = 4 * c4 + k;
+                const float xv = (c4 < pitch4 && c < d) ? x[c] : 0.0f;
+                const float hv = (c4 < pitch4 && c < d) ? h[c] : 0.0f;
+                a = fmaf(xv, hv, a);
+            }
+        }
+        acc[s] = a;
+    }
+    for (int off = lpr / 2; off >= 1; off >>= 1) {
+        float nxt[32];
+        for (int s = 0; s < lpr; ++s) nxt[s] = acc[s] + acc[s ^ off];
+        memcpy(acc, nxt, sizeof(float) * (size_t)lpr);
+    }
+    return acc[0];
+}
+
+/* Sparse stream (SparseDev, dpsvm_b200/csrc/smo_kernels.cuh): the non-zeros of the row in ascending column
+ * order are dealt round-robin to `lanes` lanes (entry e -> lane e % lanes); each lane adds its products with
+ * sequential FMAs in that order; the same xor-butterfly sums the lanes.  -0.0 counts as zero. */
+float oracle_dot_sparse_order(const float* x, const float* h, int d, int lanes)
+{
+    float acc[32] = {0};
+    int e = 0;
+    for (int c = 0; c < d; ++c) {
+        if (x[c] != 0.0f) {
+            acc[e % lanes] = fmaf(x[c], h[c], acc[e % lanes]);
+            ++e;
+        }
+    }
+    for (int off = lanes / 2; off >= 1; off >>= 1) {
+        float nxt[32];
+        for (int s = 0; s < lanes; ++s) nxt[s] = acc[s] + acc[s ^ off];
+        memcpy(acc, nxt, sizeof(float) * (size_t)lanes);
+    }
+    return acc[0];
+}
+
 int oracle_max_threads(void)
 {
 #ifdef _OPENMP

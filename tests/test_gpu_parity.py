@@ -684,3 +684,40 @@ def test_sparse_stream_edge_rows(monkeypatch):
             a, f[mode], _ = t.download()
             assert np.isfinite(f[mode]).all() and st.num_iter == 80
     assert np.abs(f["dense"] - f["sparse"]).max() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------
+# the documented summation orders, against their CPU restatement in the oracle
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,mode,lanes", [("mnist_512", "dense", 0), ("adult_2048", "dense", 0), ("odd_d_333x37", "dense", 0),
+                                             ("mnist_512", "sparse", 8), ("mnist_512", "sparse", 4), ("mnist_512", "sparse", 16),
+                                             ("mnist_512", "sparse", 32), ("adult_2048", "sparse", 4), ("odd_d_333x37", "sparse", 8)])
+@pytest.mark.parametrize("loop_flags", [0, capi.FLAG_GRAPH_LOOP])
+def test_dot_products_follow_the_documented_order_bit_for_bit(golden, oracle, monkeypatch, name, mode, lanes, loop_flags):
+    """The kernel-row cache holds the sweep's dot products <x_j, x_hi>.  Read a line back and compare EVERY entry,
+    bit for bit, with oracle_dot_dense_order / oracle_dot_sparse_order -- independent C restatements of the two
+    orders (DotGeom; SparseDev) -- and |x_i|^2 from setup with the same functions applied to (x_i, x_i)."""
+    monkeypatch.setenv("DPSVM_LAYOUT", mode)
+    if lanes:
+        monkeypatch.setenv("DPSVM_SPARSE_LANES", str(lanes))
+    g = golden(name)
+    x, n = g["x"], int(g["n"])
+
+    def dot(a, b):
+        return oracle.dot_sparse_order(a, b, lanes) if lanes else oracle.dot_dense_order(a, b)
+    with _trainer(g, cache_size=4, flags=loop_flags) as t:
+        assert t.layout_info()[0] == lanes
+        _, _, xsq = t.download(xsq=True)
+        rows = range(0, n, max(1, n // 97))
+        assert all(xsq[i] == dot(x[i], x[i]) for i in rows)
+        st = t.train(3)
+        if loop_flags:          # dpsvm_cache_lookup reads the graph loop's bookkeeping
+            for key in (st.i_hi, st.i_lo):
+                ptr, hit = t.cache_lookup(key)
+                assert hit
+                line = _device_floats(ptr, n)
+                want = np.array([dot(x[j], x[key]) for j in range(n)], np.float32)
+                assert np.array_equal(line.view(np.uint32), want.view(np.uint32)), int((line != want).sum())
+        else:                   # resident loop: same arithmetic, so the same f as the graph loop (asserted elsewhere);
+            alpha, f, _ = t.download()      # here: f after three iterations is finite and moved
+            assert np.isfinite(f).all() and (f != -g["y"]).any()

@@ -89,3 +89,27 @@ def test_lru_replay(oracle):
     #   1 miss(l0) 2 miss(l1) 1 hit 3 miss evicts 2 (l1) 2 miss evicts 1 (l0) 4 miss evicts 3 (l1) 1 miss evicts 2 (l0)
     assert hit.tolist() == [0, 0, 1, 0, 0, 0, 0] and hits == 1
     assert line.tolist() == [0, 1, 0, 1, 0, 1, 0]
+
+
+def test_dot_order_restatements(oracle):
+    """oracle_dot_dense_order / oracle_dot_sparse_order (the CUDA path's two summation orders): the reference's only
+    known-answer vector (testblas.c:21-33, 3x3 gemv -> (-1, 3, -3)) exactly, random rows to fp32 rounding, and
+    the sparse order ignores zeros (including -0.0) wherever they sit."""
+    k = dict(np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "kat_gemv3x3.npz")))
+    for r in range(3):
+        assert float(oracle.dot_dense_order(k["m"][r], k["x"])) == float(k["y"][r])
+        for lanes in (4, 8, 16, 32):
+            assert float(oracle.dot_sparse_order(k["m"][r], k["x"], lanes)) == float(k["y"][r])
+    rng = np.random.default_rng(11)
+    for d in (1, 3, 5, 37, 123, 128, 520, 784, 1100):
+        x = ((rng.random(d) < 0.4) * rng.standard_normal(d)).astype(np.float32)
+        h = rng.standard_normal(d).astype(np.float32)
+        ref = float(x.astype(np.float64) @ h.astype(np.float64))
+        scale = float(np.abs(x.astype(np.float64) * h).sum()) + 1e-30
+        assert abs(float(oracle.dot_dense_order(x, h)) - ref) < 4e-7 * scale
+        for lanes in (4, 8, 16, 32):
+            v = oracle.dot_sparse_order(x, h, lanes)
+            assert abs(float(v) - ref) < 4e-7 * scale
+            x2 = np.concatenate([np.array([-0.0, 0.0], np.float32), x, np.zeros(7, np.float32)])
+            h2 = np.concatenate([np.array([5.0, -3.0], np.float32), h, np.ones(7, np.float32)])
+            assert oracle.dot_sparse_order(x2, h2, lanes) == v
