@@ -27,6 +27,16 @@ def test_library_exports_every_declared_symbol():
     assert L.dpsvm_abi_version() == 1
 
 
+def test_binding_constants_match_the_header():
+    """Flags and status codes of the ctypes binding are the header's, value for value."""
+    text = open(os.path.join(ROOT, "include", "dpsvm_cuda.h")).read()
+    defs = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define\s+DPSVM_(FLAG_[A-Z_]+)\s+(-?\d+)", text)}
+    assert set(defs) >= {"FLAG_NO_GRAPH", "FLAG_X_SHARD_ONLY", "FLAG_GRAPH_LOOP", "FLAG_DENSE", "FLAG_SPARSE"}
+    for name, value in defs.items():
+        if name != "FLAG_NONE":
+            assert getattr(capi, name) == value, name
+
+
 def test_pitch():
     assert [capi.pitch_for(d) for d in (1, 4, 5, 123, 128, 784)] == [4, 4, 8, 124, 128, 784]
 
