@@ -15,6 +15,7 @@ HDRS      := $(wildcard $(CSRC)/*.cuh) include/dpsvm_cuda.h
 HOST      := dpsvm_b200/host
 HOST_SRCS := $(HOST)/svmTrain.cpp $(HOST)/parse.cpp $(HOST)/model_io.cpp
 HOST_LIB  := dpsvm_b200/libdpsvm_host.so
+CSV_LIB   := dpsvm_b200/libdpsvm_csv.so
 CLI       := dpsvm_b200/svmTrain
 
 REF       ?= /root/reference
@@ -43,7 +44,11 @@ $(OBJDIR)/%.o: $(CSRC)/%.cu $(HDRS)
 $(LIB): $(CU_OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(CU_OBJS) -lcudart -ldl
 
-host: $(HOST_LIB) $(CLI)
+host: $(HOST_LIB) $(CLI) $(CSV_LIB)
+
+# the CSV loader / writer alone (no SvmTrain, so no `extern state`): loadable with dlopen / ctypes
+$(CSV_LIB): $(HOST)/parse.cpp include/parse.hpp
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -pthread -shared -Iinclude -o $@ $(HOST)/parse.cpp
 
 $(HOST_LIB): $(HOST_SRCS) $(wildcard include/*.h include/*.hpp) $(LIB)
 	$(CXX) -O2 -std=c++17 -fPIC -Wall -pthread -shared -Iinclude -o $@ $(HOST_SRCS) -Ldpsvm_b200 -ldpsvm -Wl,-rpath,'$$ORIGIN'
@@ -55,7 +60,7 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -rf $(OBJDIR) $(LIB) $(HOST_LIB) $(CLI)
+	rm -rf $(OBJDIR) $(LIB) $(HOST_LIB) $(CSV_LIB) $(CLI)
 	$(MAKE) -C oracle clean
 
 .PHONY: all lib host oracle clean dropin refgpu

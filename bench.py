@@ -1,12 +1,17 @@
 #!/usr/bin/env python
-"""bench.py -- SMO iterations/s on the BASELINE.json workload, one JSON line on rank 0.
+"""bench.py -- SMO iterations/s and time-to-converge on the BASELINE.json workload, one JSON line on rank 0.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
 
-A "step" is ``iters_per_step`` SMO iterations (one fused pass over the X shard each) launched as
-CUDA-graph chunks; ``value`` = iterations/s of the whole job with X resident in HBM; ``e2e`` = the same
-metric through the public C-ABI call sequence with HOST buffers (upload of X and y from pinned
-memory, the iterations, download of alpha) inside the timed region.
+A "step" of the device-timed arm is ``iters_per_step`` SMO iterations (one fused pass over the X shard each);
+``value`` = iterations/s of the whole job with X resident in HBM.  ``e2e`` = the same metric through the public
+C-ABI call sequence with HOST buffers inside the timed region: upload of X and y from pinned memory, a whole
+training run (to convergence on the workloads that converge within a second or two, else a fixed number of
+iterations), download of alpha.  ``time_to_converge`` comes from those same runs.
+
+With N > 1 ranks the line also carries ``parity`` (sharded run against a single-GPU run of the same iterations
+on rank 0, bit for bit, with the layout pinned) and ``n1`` / ``speedup_vs_n1`` (the same workload timed on rank 0
+alone in the same process).
 
 ``--impl reference`` times the reference's own sequential CPU implementation (oracle/_ref, built from
 /root/reference/seq.cpp; falls back to the oracle port) on the same workload, rank 0 only.
@@ -19,6 +24,7 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -34,6 +40,7 @@ WORKLOADS = {
     "mnist1m": (1000000, 784),
     "blobs4m": (4000000, 128),
 }
+CONVERGES_FAST = ("mnist60k", "adult32k")      # a whole training run is a second or two: e2e and time-to-converge train to the end
 
 
 def parse_args():
@@ -47,8 +54,12 @@ def parse_args():
     ap.add_argument("--iters-per-step", type=int, default=256)
     ap.add_argument("--cache-size", type=int, default=10, help="kernel-row cache lines (reference default 10)")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--converge", type=int, default=-1, help="1/0: train to convergence in the e2e runs (default: only the workloads that converge in seconds)")
+    ap.add_argument("--parity-iters", type=int, default=2000, help="iterations of the N>1 bit-identity check (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pass-only", action="store_true")
+    ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-n1", action="store_true", help="N>1: skip the single-GPU run of the same workload on rank 0")
     return ap.parse_args()
 
 
@@ -127,6 +138,17 @@ def load_workload(args, rank=0, world=1, shard_only=False):
     return x, y, prm, n_total, d, n_total, 0
 
 
+def workload_config(args, n_total, d, prm):
+    """The `config` object: what is being solved.  Identical in both arms (ours / --impl reference); everything
+    that describes HOW a run went is under `run`."""
+    return {
+        "workload": "%s %dx%d RBF c=%g gamma=%g eps=%g" % (args.workload, n_total, d, prm["c"], prm["gamma"], prm["epsilon"]),
+        "cache_lines": args.cache_size,
+        "l2": "nothing is flushed between iterations: every SMO iteration re-reads the same X by construction; whether one "
+              "sweep exceeds the GPU's 126 MB L2 is stated under run.l2 (GPU arm)",
+    }
+
+
 def algorithmic_bytes(n, d, cache_lines, nnz=None):
     """X shard once + |x|^2, f read, f write, alpha, y at 4 B each (logical d); the two
     cache-line stores of a miss/miss iteration add 8 n when the kernel-row cache is on.
@@ -165,8 +187,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "%s %dx%d RBF c=%g gamma=%g eps=%g" % (args.workload, n_total, d, prm["c"], prm["gamma"], prm["epsilon"]),
-                   "iters_per_step": ips},
+        "config": workload_config(args, n_total, d, prm),
+        "run": {"iters_per_step": ips, "rows": n_total, "program": "seq.cpp (sequential SMO, no kernel-row cache: -s does not apply)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample,
                          "host_cores_available": os.cpu_count()},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -192,6 +214,57 @@ def cpu_baseline(x, y, prm, budget_iters=16):
                       "(single-threaded program; 1 of %d host cores)" % (iters, x.shape[0], x.shape[1], dt, os.cpu_count())}
 
 
+def ref_gpu_baseline(args, x, y, prm, cap=4000):
+    """the reference's OWN GPU path (svmTrain.cu + cache.cu: cuBLAS gemv + Thrust), rebuilt unmodified for
+    sm_100a as oracle/_ref/svmTrain_refgpu, on the same rows through a CSV file; loop time between its "SETUP DONE" and
+    "TOTAL TIME TAKEN" lines, first `cap` iterations."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "svmTrain_refgpu")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/svmTrain_refgpu not built (make refgpu needs /root/reference)"}
+    from dpsvm_b200 import datagen
+    import tempfile
+    tmp = tempfile.mkdtemp(prefix="dpsvm_refgpu_")
+    csv = os.path.join(tmp, "train.csv")
+    try:
+        datagen.write_csv(csv, x, y)
+        cmd = ["stdbuf", "-oL", exe, "-a", str(x.shape[1]), "-x", str(x.shape[0]), "-f", csv, "-c", "%g" % prm["c"], "-g", "%g" % prm["gamma"],
+               "-e", "%g" % prm["epsilon"], "-n", str(cap), "-s", str(max(args.cache_size, 2)), "-m", os.path.join(tmp, "model.txt")]
+        p = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, bufsize=1)
+        t_setup = t_total = iters = None
+        for line in p.stdout:
+            now = time.perf_counter()
+            if line.startswith("SETUP DONE"):
+                t_setup = now
+            elif line.startswith("TOTAL TIME TAKEN"):
+                t_total = now
+            elif "iteration number" in line or "Could not converge in" in line:
+                iters = int([w for w in line.replace(".", " ").split() if w.isdigit()][0])
+        p.wait(timeout=600)
+        if p.returncode != 0 or not (t_setup and t_total and iters):
+            return {"unavailable": "svmTrain_refgpu exited with %s" % p.returncode}
+        secs = t_total - t_setup
+        return {"value": iters / secs, "unit": UNIT, "iterations": iters, "loop_seconds": secs,
+                "what": "the reference's own GPU path (svmTrain.cu + cache.cu, cuBLAS sgemv + Thrust reductions, host loop), compiled "
+                        "unmodified for sm_100a, same rows via CSV, first %d iterations, wall clock between its SETUP DONE and TOTAL TIME "
+                        "TAKEN lines (includes its final accuracy print)" % cap}
+    except Exception as e:      # a comparison leg must never cost the bench line
+        return {"unavailable": "%s: %s" % (type(e).__name__, e)}
+    finally:
+        for f in ("train.csv", "model.txt"):
+            try:
+                os.remove(os.path.join(tmp, f))
+            except OSError:
+                pass
+        try:
+            os.rmdir(tmp)
+        except OSError:
+            pass
+
+
+def _crc(a):
+    return zlib.crc32(np.ascontiguousarray(a).view(np.uint8))
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -214,15 +287,22 @@ def main():
     x, y, prm, n_total, d, n_shard, row0 = load_workload(args, rank, world, shard_only=True)
     ips = args.iters_per_step
     max_iter = 2 ** 31 - 2
-    flags = capi.FLAG_X_SHARD_ONLY if world > 1 else 0
-    tr = capi.Trainer(n_total, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=max_iter, cache_size=args.cache_size,
-                      shard_rows=n_shard, shard_start=row0, device=local_rank, flags=flags)
-    hx = torch.from_numpy(x).pin_memory()
-    hy = torch.from_numpy(y).pin_memory()
-    if world > 1:
+
+    def make_trainer(extra_flags=0, single=False):
+        """A trainer for this rank's shard (joined to the other ranks), or -- single -- for the whole set on this GPU."""
+        if single or world == 1:
+            return capi.Trainer(n_total, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=max_iter, cache_size=args.cache_size,
+                                device=local_rank, flags=extra_flags)
+        t = capi.Trainer(n_total, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=max_iter, cache_size=args.cache_size,
+                         shard_rows=n_shard, shard_start=row0, device=local_rank, flags=capi.FLAG_X_SHARD_ONLY | extra_flags)
         ids = [capi.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
-        tr.comm_init(ids[0], rank, world)
+        t.comm_init(ids[0], rank, world)
+        return t
+
+    tr = make_trainer()
+    hx = torch.from_numpy(x).pin_memory()
+    hy = torch.from_numpy(y).pin_memory()
     tr.upload(hx, hy)
 
     stream = torch.cuda.ExternalStream(tr.stream)
@@ -235,33 +315,49 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident arm -----------------------------------------------------------------
-    for _ in range(args.warmup):
-        tr.train_async(ips)
-    st_w = tr.sync()
-    clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
-    barrier()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        tr.train_async(ips)
-    ev1.record(stream)
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    clk = clocks.stop() if rank == 0 else None
-    st = tr.sync()
-    done_iters = st.num_iter - st_w.num_iter
-    if world > 1:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return int(t.item())
+
+    def timed_iterations(t, steps, warmup, sample_clocks=False):
+        """`steps` x ips iterations on the trainer's stream between CUDA events, after `warmup` untimed steps."""
+        s = torch.cuda.ExternalStream(t.stream)
+        for _ in range(warmup):
+            t.train_async(ips)
+        st_w = t.sync()
+        clocks = ClockSampler(local_rank) if sample_clocks else None
+        if clocks:
+            clocks.start()
+        barrier()
+        ev0.record(s)
+        for _ in range(steps):
+            t.train_async(ips)
+        ev1.record(s)
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clk = clocks.stop() if clocks else None
+        st = t.sync()
+        return ms, st.num_iter - st_w.num_iter, st, clk
+
+    # ---- device-resident arm -----------------------------------------------------------------
+    ms, done_iters, st, clk = timed_iterations(tr, args.steps, args.warmup, sample_clocks=(rank == 0))
+    ms = max_over_ranks(ms)
     value = done_iters / (ms * 1e-3)
 
     # ---- the dominant kernel alone (stateless launcher, back to back on one stream) -----------
     pass_ms = None
     lanes, nnz, sweep_bytes = tr.layout_info()
-    if not args.no_pass_only and lanes == 0:        # the stateless pass entry point sweeps dense rows
+    if not args.no_pass_only and lanes == 0 and world == 1:        # the stateless pass entry point sweeps dense rows
         s = tr.device_state()
         pitch = s["pitch"]
         keys = torch.full((2,), -1, dtype=torch.int64, device="cuda")
@@ -304,25 +400,121 @@ def main():
         pass_ms = e0.elapsed_time(e1) / reps
 
     # ---- end to end: host buffers in, host buffers out, every step ------------------------------
-    e2e_iters = max(ips, 1024)          # a training run is tens of thousands of iterations per upload; 1024 is conservative
-    e2e_t = []
+    # One e2e step is one whole job as a user runs it: dpsvm_upload -> dpsvm_train -> dpsvm_download.
+    to_convergence = (args.workload in CONVERGES_FAST and not args.rows) if args.converge < 0 else bool(args.converge)
+    e2e_cap = 0 if to_convergence else max(ips, 1024)
+    e2e_runs = []
     for k in range(args.e2e_steps + 1):
         barrier()
         t0 = time.perf_counter()
-        tr.upload(hx, hy)                 # H2D of X and y from pinned host memory, |x|^2, first selection
-        tr.train_async(e2e_iters)
+        tr.upload(hx, hy)                 # H2D of X and y from pinned host memory, |x|^2, sparse stream, first selection
+        t1 = time.perf_counter()
+        st_e = tr.train(e2e_cap)          # the loop, to convergence (or e2e_cap iterations)
+        t2 = time.perf_counter()
         alpha, _, _ = tr.download(alpha=True, f=False)    # D2H of alpha (synchronises)
-        st_e = tr.sync()
         barrier()
+        t3 = time.perf_counter()
         if k > 0:                          # first one is a warm-up
-            e2e_t.append(time.perf_counter() - t0)
-        assert st_e.num_iter == e2e_iters or st_e.converged
-    e2e_s = max(e2e_t)
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+            e2e_runs.append((t3 - t0, t2 - t1, t1 - t0, st_e.num_iter, st_e.converged, st_e.b))
+        assert st_e.converged or st_e.num_iter == e2e_cap
+    e2e_runs.sort()
+    e2e_s, train_s, upload_s, e2e_iters, e2e_conv, e2e_b = e2e_runs[-1]        # the worst run
+    e2e_s = max_over_ranks(e2e_s)
+    train_s = max_over_ranks(train_s)
     e2e_value = e2e_iters / e2e_s
+    n_sv = sum_over_ranks(int((alpha > 0).sum()))
+    n_bound = sum_over_ranks(int((alpha == np.float32(prm["c"])).sum()))
+    st_last = tr.sync()
+    time_to_converge = {
+        "seconds": train_s, "seconds_with_upload_and_download": e2e_s, "upload_and_setup_seconds": max_over_ranks(upload_s),
+        "iterations": int(e2e_iters), "converged": bool(e2e_conv), "n_sv": n_sv, "n_sv_at_c": n_bound, "b": float(e2e_b),
+        "cache_lines": args.cache_size, "cache_hits": int(st_last.cache_hits), "cache_lookups": int(st_last.cache_lookups),
+        "what": ("one dpsvm_train call from alpha = 0 to b_lo <= b_hi + 2 eps (svmTrainMain.cpp:235-310), X resident; wall clock, "
+                 "worst of %d runs, max over ranks" % args.e2e_steps) if to_convergence else
+                ("NOT run to convergence on this workload by default (--converge 1 does): first %d iterations" % e2e_cap),
+    }
+
+    # ---- N > 1: the same workload on ONE GPU in the same process (rank 0), and bit-identity of the sharded run ----
+    parity = None
+    n1 = None
+    if world > 1 and not (args.no_n1 and args.parity_iters <= 0):
+        pitch = capi.pitch_for(d)
+        size, disp = capi.shard_layout(n_total, world)
+        # rank 0 collects every shard over NCCL into one device buffer (no second host copy of the whole set)
+        mine = torch.zeros(n_shard, pitch, dtype=torch.float32, device="cuda")
+        mine[:, :d] = hx.cuda()
+        ymine = hy.cuda()
+        full_x = full_y = None
+        if rank == 0:
+            full_x = torch.empty(n_total, pitch, dtype=torch.float32, device="cuda")
+            full_y = torch.empty(n_total, dtype=torch.int32, device="cuda")
+            full_x[:n_shard] = mine
+            full_y[:n_shard] = ymine
+            for r in range(1, world):
+                dist.recv(full_x[int(disp[r]):int(disp[r]) + int(size[r])], src=r)
+                dist.recv(full_y[int(disp[r]):int(disp[r]) + int(size[r])], src=r)
+        else:
+            dist.send(mine, dst=0)
+            dist.send(ymine, dst=0)
+        del mine
+        barrier()
+
+        if not args.no_n1 and rank == 0:
+            with make_trainer(single=True) as t1:
+                t1.upload_device(full_x, pitch, full_y)
+                steps1 = max(3, args.steps // 2)
+                ms1, it1, _, _ = timed_iterations_single(torch, t1, ips, steps1, 3)
+                l1, _, sb1 = t1.layout_info()
+                n1 = {"value": it1 / (ms1 * 1e-3), "unit": UNIT, "us_per_iteration": 1e3 * ms1 / max(it1, 1), "steps": steps1,
+                      "layout": ("sparse stream, %d lanes" % l1) if l1 else "dense rows", "sweep_MB": 1e-6 * sb1,
+                      "what": "the same workload on rank 0's GPU alone, same process, X resident, CUDA events"}
+        barrier()
+
+        if args.parity_iters > 0:
+            k_par = args.parity_iters
+            dense_frac = float(np.count_nonzero(x)) / max(1, x.size)
+            pins = [("dense rows", capi.FLAG_DENSE, None)]
+            if dense_frac < 0.7 and d <= 1024:
+                pins.append(("sparse stream, 8 lanes per row", capi.FLAG_SPARSE, "8"))
+            checks = []
+            for name, flag, lanes_env in pins:
+                old = os.environ.get("DPSVM_SPARSE_LANES")
+                if lanes_env:
+                    os.environ["DPSVM_SPARSE_LANES"] = lanes_env
+                with make_trainer(extra_flags=flag) as tp:
+                    tp.upload(hx, hy)
+                    sp = tp.train(k_par)
+                    a_p, f_p, _ = tp.download()
+                    rec = (int(sp.num_iter), float(sp.b_hi), float(sp.b_lo), int(sp.i_hi), int(sp.i_lo), _crc(a_p), _crc(f_p),
+                           row0, n_shard, tp.comm_transport, bool(tp.loop_info()[0]))
+                recs = [None] * world
+                dist.all_gather_object(recs, rec)
+                ok = None
+                if rank == 0:
+                    with make_trainer(extra_flags=flag, single=True) as ts:
+                        ts.upload_device(full_x, pitch, full_y)
+                        ss = ts.train(k_par)
+                        a_s, f_s, _ = ts.download()
+                    ok = True
+                    for r in recs:
+                        lo, cnt = r[7], r[8]
+                        ok = ok and r[:5] == (int(ss.num_iter), float(ss.b_hi), float(ss.b_lo), int(ss.i_hi), int(ss.i_lo))
+                        ok = ok and r[5] == _crc(a_s[lo:lo + cnt]) and r[6] == _crc(f_s[lo:lo + cnt])
+                    checks.append({"layout": name, "bit_identical": bool(ok), "iterations": int(ss.num_iter),
+                                   "pair_of_last_iteration": [int(ss.i_hi), int(ss.i_lo)], "exchange": recs[0][9],
+                                   "loop": "resident" if recs[0][10] else "graph"})
+                if lanes_env:
+                    if old is None:
+                        os.environ.pop("DPSVM_SPARSE_LANES", None)
+                    else:
+                        os.environ["DPSVM_SPARSE_LANES"] = old
+                barrier()
+            if rank == 0:
+                parity = {"checked": True, "bit_identical": all(c["bit_identical"] for c in checks), "k": k_par, "runs": checks,
+                          "what": "every rank trains k iterations on its shard with the layout pinned; rank 0 repeats the same k iterations "
+                                  "on ONE GPU holding the whole set; per rank (num_iter, b_hi, b_lo, i_hi, i_lo) are compared and the CRC-32 "
+                                  "of the alpha and f shards against the same slices of the single-GPU arrays"}
+        del full_x, full_y
 
     if rank != 0:
         tr.close()
@@ -331,15 +523,17 @@ def main():
         return
 
     peak, peak_src = measured_peak()
-    abytes = algorithmic_bytes(n_shard, d, args.cache_size, nnz if lanes else None)
+    stream_abytes = algorithmic_bytes(n_shard, d, args.cache_size, nnz if lanes else None)
     dense_abytes = algorithmic_bytes(n_shard, d, args.cache_size)
     iter_ms = ms / max(done_iters, 1)
-    traffic = None
+    traffic, traffic_src = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
-            key = "%s%s_per_iteration" % (args.workload, "_sparse" if lanes else "")
-            per_iter = json.load(fh).get(key if world == 1 else "%s%s_p%d_per_iteration" % (args.workload, "_sparse" if lanes else "", world))
-            traffic = per_iter
+            tj = json.load(fh)
+        key = "%s%s%s" % (args.workload, "_sparse" if lanes else "", "" if world == 1 else "_p%d" % world)
+        ent = tj.get("entries", {}).get(key)
+        if ent:
+            traffic, traffic_src = float(ent["dram_bytes_per_iteration"]), {k: ent.get(k) for k in ("commit", "source")}
     except Exception:
         pass
     resident, chunk = tr.loop_info()
@@ -348,7 +542,7 @@ def main():
         launches = args.steps * ((ips + chunk - 1) // chunk)
         kernel_name = "smo_resident_kernel"
         kernel_ms = ms / launches
-        bytes_per_launch = abytes * done_iters / launches
+        iters_per_launch = done_iters / launches
         timing = ("the timed region itself: %d launches of %d iterations each, CUDA events on the launching stream "
                   "(max over ranks)" % (launches, chunk))
         share = 1.0
@@ -357,22 +551,28 @@ def main():
         kernels_per_iter = 3 if tr.comm_transport == "nccl" else 2     # control + pass (+ pack before the NCCL all-gather)
         kernel_name = "smo_pass_sparse_kernel" if lanes else "smo_pass_kernel"
         kernel_ms = pass_ms if pass_ms is not None else iter_ms
-        bytes_per_launch = abytes
+        iters_per_launch = 1.0
         timing = ("pass kernel alone: 200 launches replayed from one CUDA graph with the trainer's L2 policy and sweep order, "
                   "CUDA events on the replay stream") if pass_ms is not None else "whole iteration (control + pass) from the timed region"
         share = (kernel_ms / iter_ms) if pass_ms is not None else 1.0
         gpu_launches = int(done_iters * kernels_per_iter)
-    achieved = bytes_per_launch / (kernel_ms * 1e-3) / 1e9
-    if traffic is not None:
-        traffic = traffic * (bytes_per_launch / abytes)      # ncu DRAM bytes per iteration x iterations per launch
+    # SURVEY 8(d) basis (dense rows, 4 n d + 20 n): the figure `achieved` is defined on.  When the sweep reads the sparse
+    # stream instead, the same time also gives the stream's own bytes (6 B per non-zero): both fractions are reported.
+    achieved = dense_abytes * iters_per_launch / (kernel_ms * 1e-3) / 1e9
+    achieved_stream = stream_abytes * iters_per_launch / (kernel_ms * 1e-3) / 1e9
+    on_chip = (not lanes) and sweep_bytes <= 30e6
+    if lanes:
+        bound = "l2+lsu" if sweep_bytes <= 126e6 else "hbm"
+    else:
+        bound = "smem" if on_chip else "hbm"
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {
-            "workload": "%s %dx%d RBF c=%g gamma=%g eps=%g" % (args.workload, n_total, d, prm["c"], prm["gamma"], prm["epsilon"]),
+        "config": workload_config(args, n_total, d, prm),
+        "run": {
             "iters_per_step": ips, "iterations_timed": done_iters, "converged_during_timing": bool(st.converged),
-            "cache_lines": args.cache_size, "cache_hits": int(st.cache_hits), "cache_lookups": int(st.cache_lookups),
+            "cache_hits": int(st.cache_hits), "cache_lookups": int(st.cache_lookups),
             "rows_per_gpu": n_shard, "us_per_iteration": 1e3 * iter_ms, "exchange": tr.comm_transport,
             "loop": "resident (persistent cooperative kernel, %d iterations per launch)" % chunk if resident
                     else "CUDA graph of [control, pass] x %d" % chunk,
@@ -380,31 +580,67 @@ def main():
             "layout": ("sparse stream, %d lanes per row: %.1f %% of the cells are non-zero, %.1f MB per sweep (padding included) instead of %.1f MB of dense rows"
                        % (lanes, 100.0 * nnz / (n_shard * d), 1e-6 * sweep_bytes, 4e-6 * n_shard * d)) if lanes
                       else "dense rows, %.1f MB per sweep" % (1e-6 * sweep_bytes),
-            "l2": "%.1f MB per sweep vs 126 MB L2: %s; consecutive iterations sweep in opposite directions, nothing is flushed between them (the loop re-reads the same X by construction)"
+            "l2": "%.1f MB per sweep vs 126 MB L2: %s; consecutive iterations sweep in opposite directions"
                   % (1e-6 * sweep_bytes, "inputs larger than L2" if sweep_bytes > 126e6 else "L2-resident"),
-            "iteration_GBps_incl_control": abytes / (iter_ms * 1e-3) / 1e9,
         },
-        "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_iteration": abytes,
-                     "algorithmic_bytes_basis": ("sparse stream: 6 B per non-zero + 20 B per row (+ 8 B per row of cache-line stores)" if lanes
-                                                 else "SURVEY 8(d): 4 n d + 20 n (+ 8 n of cache-line stores)"),
-                     "dense_rows_equivalent_GBps": dense_abytes / (iter_ms * 1e-3) / 1e9,
-                     "note": ("the sparse sweep is limited by its shared-memory gathers (LSU), and a stream of up to ~120 MB is served from L2 "
-                              "and shared memory, not HBM (profiles/r01_sparse_ncu_summary.md); frac is still quoted against the HBM copy peak") if lanes else None,
-                     "kernel_us": 1e3 * kernel_ms, "timing": timing, "share_of_step": share},
+        "roofline": {"bound": bound, "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": (traffic * iters_per_launch) if traffic is not None else None,
+                     "traffic_source": traffic_src, "peak_source": peak_src,
+                     "algorithmic_bytes_basis": "SURVEY 8(d): 4 n d + 20 n per iteration (+ 8 n of cache-line stores), dense rows, logical d",
+                     "algorithmic_bytes_per_iteration": dense_abytes, "algorithmic_bytes_per_launch": dense_abytes * iters_per_launch,
+                     "frac_dense_basis": achieved / peak,
+                     "frac_stream_basis": (achieved_stream / peak) if lanes else None,
+                     "stream_bytes_per_iteration": stream_abytes if lanes else None,
+                     "note": ("the sweep reads the sparse stream (6 B per non-zero, zeros skipped), so on the dense-row basis the figure can exceed "
+                              "the HBM peak; a stream of up to ~120 MB is served from L2 and shared memory and the binding units are the "
+                              "shared-memory gathers (LSU) and the L2->SM fabric, not HBM -- `bound` says which; frac_stream_basis counts only "
+                              "the bytes the kernel is asked to read") if lanes else
+                             ("the whole shard is held in shared memory across iterations: nothing streams from HBM" if on_chip else None),
+                     "kernel_us": 1e3 * kernel_ms, "iterations_per_launch": iters_per_launch, "timing": timing, "share_of_step": share},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(4 * n_shard * d + 4 * n_shard),
-                "d2h_bytes_per_step": int(4 * n_shard + 64), "iters_per_step": e2e_iters,
-                "what": "dpsvm_upload (X,y from pinned host) + dpsvm_train_async + dpsvm_download(alpha) + dpsvm_sync, wall clock, worst of %d" % args.e2e_steps},
+                "d2h_bytes_per_step": int(4 * n_shard + 2 * 128), "iters_per_step": int(e2e_iters), "seconds_per_step": e2e_s,
+                "what": "one e2e step = one whole job through the C ABI with host buffers: dpsvm_upload (X, y from pinned host memory; |x|^2, "
+                        "sparse stream, first selection) + dpsvm_train (%s) + dpsvm_download(alpha); wall clock, worst of %d, max over ranks.  "
+                        "Not the 256-iteration step of `value`: a job uploads X once and then iterates"
+                        % ("to convergence" if to_convergence else "%d iterations" % e2e_cap, args.e2e_steps)},
+        "time_to_converge": time_to_converge,
         "gpu_launches": gpu_launches,
         "clocks": clk,
     }
+    if parity is not None:
+        out["parity"] = parity
+    if n1 is not None:
+        out["n1"] = n1
+        out["speedup_vs_n1"] = value / n1["value"]
+    if world == 1 and not args.no_ref_gpu and not args.rows and args.workload in CONVERGES_FAST:
+        tr.close()
+        tr = None
+        out["ref_gpu_baseline"] = ref_gpu_baseline(args, x, y, prm)
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(x, y, prm)
     print(json.dumps(out), flush=True)
-    tr.close()
+    if tr is not None:
+        tr.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def timed_iterations_single(torch, t, ips, steps, warmup):
+    """rank 0 alone (no collective inside): `steps` x ips iterations between CUDA events on the trainer's stream."""
+    s = torch.cuda.ExternalStream(t.stream)
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    for _ in range(warmup):
+        t.train_async(ips)
+    st_w = t.sync()
+    torch.cuda.synchronize()
+    e0.record(s)
+    for _ in range(steps):
+        t.train_async(ips)
+    e1.record(s)
+    torch.cuda.synchronize()
+    st = t.sync()
+    return e0.elapsed_time(e1), st.num_iter - st_w.num_iter, st, None
 
 
 if __name__ == "__main__":

@@ -32,6 +32,8 @@ int fail(int code, const char* fmt, ...)
                         "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));       \
     } while (0)
 
+static inline bool misaligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
+
 static int env_int(const char* name, int dflt)
 {
     const char* v = getenv(name);
@@ -47,7 +49,7 @@ static void free_all(dpsvm_ctx* c)
     cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_keys_copy); cudaFree(c->d_st);
     cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
     cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
-    cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru);
+    cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru); cudaFree(c->d_trace);
     sparse_release(c);
     predict_free(c);
     comm_free(c);
@@ -172,6 +174,8 @@ static int ensure_cache_path(dpsvm_ctx* c, int path)
     return DPSVM_OK;
 }
 
+constexpr int kResidentRefused = -1000;     // internal: launch_resident was refused before anything ran
+
 static int launch_resident_chunk(dpsvm_ctx* c)
 {
     int rc = ensure_cache_path(c, 2);
@@ -189,6 +193,7 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.gamma = c->p.gamma; a.c = c->p.c; a.epsilon = c->p.epsilon;
     a.max_iter = c->p.max_iter;
     a.index_base = c->p.shard_start;
+    a.empty_row = c->res0;
     a.st = c->d_st;
     a.keys = c->d_keys;
     a.slots = c->d_slots;
@@ -203,12 +208,22 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.sp = c->sp;
     a.world = 1;
     if (c->world > 1 && !comm_fill_resident(c, &a)) return fail(DPSVM_ERR_STATE, "resident loop needs the peer-memory exchange");
-    static unsigned long long* d_trace = nullptr;
     const int trace_on = env_int("DPSVM_TRACE", 0);
-    if (trace_on && !d_trace) { CU(cudaMalloc(&d_trace, sizeof(unsigned long long) * 8 * 1024)); CU(cudaMemset(d_trace, 0, sizeof(unsigned long long) * 8 * 1024)); }
+    if (trace_on && !c->d_trace) { CU(cudaMalloc(&c->d_trace, sizeof(unsigned long long) * 8 * 1024)); CU(cudaMemset(c->d_trace, 0, sizeof(unsigned long long) * 8 * 1024)); }
+    unsigned long long* d_trace = c->d_trace;
     a.trace = trace_on ? d_trace : nullptr;
     a.trace_iter = env_int("DPSVM_TRACE_ITER", 20);
-    CU(launch_resident(a, variant_for(c, (int)(c->launched_iters & 1)), c->stream));
+    {
+        const cudaError_t e = env_int("DPSVM_FAULT_RESIDENT_LAUNCH", 0) ? cudaErrorCooperativeLaunchTooLarge       // fault injection (tests)
+                                                                       : launch_resident(a, variant_for(c, (int)(c->launched_iters & 1)), c->stream);
+        if (e != cudaSuccess) {
+            // a launch-time refusal (cooperative launch unavailable under MPS/MIG, shared-memory budget, grid that is not
+            // co-resident): nothing has run; the caller may fall back to the graph loop, which is bit-identical
+            cudaGetLastError();
+            fail(DPSVM_ERR_CUDA, "resident loop launch -> %s", cudaGetErrorString(e));
+            return kResidentRefused;
+        }
+    }
     c->launched_iters += c->chunk;
     if (trace_on && c->launched_iters == (long long)c->chunk * trace_on) {
         // debugging aid: phase times of one iteration, per CTA (chain | sweep | barrier wait), in us
@@ -248,7 +263,14 @@ static int launch_resident_chunk(dpsvm_ctx* c)
 
 static int launch_chunk(dpsvm_ctx* c)
 {
-    if (c->loop_resident && (c->world == 1 || c->exchange_p2p)) return launch_resident_chunk(c);
+    if (c->loop_resident && (c->world == 1 || c->exchange_p2p)) {
+        const int rc = launch_resident_chunk(c);
+        if (rc != kResidentRefused) return rc;
+        // single GPU: carry on with the graph loop from the same state (the two loops are interchangeable).  Several
+        // GPUs: every rank must run the same loop (they share the mailboxes' sequence numbers), so report the error.
+        if (c->world > 1) return DPSVM_ERR_CUDA;
+        c->loop_resident = 0;
+    }
     {
         int rc = ensure_cache_path(c, 1);
         if (rc != DPSVM_OK) return rc;
@@ -340,6 +362,7 @@ int dpsvm_abi_version(void) { return DPSVM_ABI_VERSION; }
 int dpsvm_row_norms(const float* d_x, int n, int d, int pitch, float* d_xsq, void* stream)
 {
     if (!d_x || !d_xsq || n < 0 || d <= 0 || pitch < d || pitch % 4) return fail(DPSVM_ERR_INVALID, "dpsvm_row_norms: bad arguments");
+    if (misaligned16(d_x)) return fail(DPSVM_ERR_INVALID, "dpsvm_row_norms: d_x must be 16-byte aligned (rows are read as 128-bit words)");
     CU(launch_row_norms(d_x, n, pitch, d_xsq, (cudaStream_t)stream));
     return DPSVM_OK;
 }
@@ -365,6 +388,8 @@ int dpsvm_smo_pass(const dpsvm_pass_args* g, void* stream)
         return fail(DPSVM_ERR_INVALID, "dpsvm_smo_pass: null pointer");
     if (g->n < 0 || g->d <= 0 || g->pitch < g->d || g->pitch % 4)
         return fail(DPSVM_ERR_INVALID, "dpsvm_smo_pass: bad shape (pitch must be a multiple of 4 and >= d)");
+    if (misaligned16(g->d_x) || misaligned16(g->d_x_hi) || misaligned16(g->d_x_lo))
+        return fail(DPSVM_ERR_INVALID, "dpsvm_smo_pass: d_x, d_x_hi and d_x_lo must be 16-byte aligned (128-bit loads, TMA bulk copies)");
     PassDev a{};
     a.x4 = reinterpret_cast<const float4*>(g->d_x);
     a.n = g->n; a.pitch4 = g->pitch / 4;

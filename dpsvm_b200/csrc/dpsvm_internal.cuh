@@ -55,6 +55,7 @@ struct dpsvm_ctx {
     int* d_lru = nullptr;        // [kResCacheLines keys][kResCacheLines stamps][2 meta]
     int cache_path = 0;          // which loop last owned the kernel-row cache: 0 none, 1 graph/split, 2 resident
     long long launched_iters = 0;
+    unsigned long long* d_trace = nullptr;   // DPSVM_TRACE: per-CTA phase stamps of one iteration (debugging aid)
 
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t gexec = nullptr;

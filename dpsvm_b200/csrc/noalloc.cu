@@ -91,6 +91,8 @@ extern "C" int dpsvm_smo_iteration_noalloc(const dpsvm_iteration_args* g, void* 
         return fail(DPSVM_ERR_INVALID, "dpsvm_smo_iteration_noalloc: null pointer");
     if (g->n <= 0 || g->d <= 0 || g->pitch < g->d || g->pitch % 4)
         return fail(DPSVM_ERR_INVALID, "dpsvm_smo_iteration_noalloc: bad shape (n > 0, pitch a multiple of 4 and >= d)");
+    if ((reinterpret_cast<uintptr_t>(g->d_x) & 15u) != 0)
+        return fail(DPSVM_ERR_INVALID, "dpsvm_smo_iteration_noalloc: d_x must be 16-byte aligned (rows are read as 128-bit words)");
     if (g->pitch > DPSVM_NOALLOC_MAX_PITCH)
         return fail(DPSVM_ERR_LIMIT,
                     "dpsvm_smo_iteration_noalloc: row pitch %d floats exceeds the built-in work area (DPSVM_NOALLOC_MAX_PITCH = %d); "

@@ -611,6 +611,10 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
     } else {
         unpack_key_up(k_up, &b_hi, &i_hi);
         unpack_key_low(k_low, &b_lo, &i_lo);
+        // An empty set decodes to the reference's default, global row 0 (svmTrainMain.cpp:249-252).  When the rows
+        // held here start at res0 > 0 that row is not resident: the first resident row stands in for it.
+        if (k_up == DPSVM_KEY_EMPTY) i_hi = a.res0;
+        if (k_low == DPSVM_KEY_EMPTY) i_lo = a.res0;
     }
     const int r_hi = i_hi - a.res0, r_lo = i_lo - a.res0;
     const float* src_hi = a.ext_row_hi ? a.ext_row_hi : a.x + (size_t)r_hi * a.pitch;

@@ -181,6 +181,7 @@ struct ResidentDev {
     float* f;                   // [n]
     float gamma, c, epsilon;
     int max_iter, index_base;
+    int empty_row;              // global row an empty I-set decodes to: the first RESIDENT row (row 0 when X is held from row 0)
     DevState* st;
     unsigned long long* keys;   // [2] selection in (launch) / out (exit)
     ResSlot* slots;             // [2][grid]

@@ -237,6 +237,10 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const unsigned long long k_up = a.keys[0], k_low = a.keys[1];
         unpack_key_up(k_up, &b_hi, &i_hi);
         unpack_key_low(k_low, &b_lo, &i_lo);
+        // empty set: the reference's default is global row 0 (svmTrainMain.cpp:249-252); the first owned row stands
+        // in for it when the rows resident here start later (same rule as smo_control_kernel)
+        if (k_up == DPSVM_KEY_EMPTY) i_hi = a.empty_row;
+        if (k_low == DPSVM_KEY_EMPTY) i_lo = a.empty_row;
         a_hi_old = a.alpha[i_hi - a.index_base];
         a_lo_old = a.alpha[i_lo - a.index_base];
     }
@@ -604,6 +608,10 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             unpack_key_low(nxt_low.key, &b_lo, &i_lo);
             a_hi_old = nxt_up.alpha;
             a_lo_old = nxt_low.alpha;
+            // an empty set has no candidate row: default row and ITS alpha, exactly as at launch and in the graph loop
+            // (the owner's store of this iteration is ordered before the grid barrier above)
+            if (nxt_up.key == DPSVM_KEY_EMPTY) { i_hi = a.empty_row; a_hi_old = __ldcg(a.alpha + (a.empty_row - a.index_base)); }
+            if (nxt_low.key == DPSVM_KEY_EMPTY) { i_lo = a.empty_row; a_lo_old = __ldcg(a.alpha + (a.empty_row - a.index_base)); }
         }
         // (s_cand is next written after a whole sweep, with several block barriers in between)
     }

@@ -95,14 +95,16 @@ def blobs(n: int, d: int = 128, seed: int = 3, row0: int = 0, clusters: int = 32
 
 
 def write_csv(path: str, x: np.ndarray, y: np.ndarray) -> None:
-    """`label,f0,...,f{d-1}` per line -- the layout parse.cpp:10-43 reads.  %.9g round-trips fp32
-    through stof()."""
-    with open(path, "w") as fh:
-        for i in range(x.shape[0]):
-            fh.write(str(int(y[i])))
-            fh.write(",")
-            fh.write(",".join("%.9g" % v for v in x[i]))
-            fh.write("\n")
+    """`label,f0,...,f{d-1}` per line -- the layout parse.cpp:10-43 reads; values round-trip fp32 bit for bit
+    through stof().  Written by the host library's multi-threaded writer (dpsvm_host_write_csv)."""
+    import ctypes
+    import os
+    lib = ctypes.CDLL(os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdpsvm_csv.so"))
+    lib.dpsvm_host_write_csv.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+    x = np.ascontiguousarray(x, np.float32)
+    y = np.ascontiguousarray(y, np.int32)
+    if lib.dpsvm_host_write_csv(path.encode(), x.ctypes.data, y.ctypes.data, x.shape[0], x.shape[1]) != 0:
+        raise OSError("could not write " + path)
 
 
 def make(workload: str, n: int | None = None, seed: int | None = None, row0: int = 0):

@@ -190,3 +190,49 @@ void populate_data_rows(vector<float>& x, vector<int>& y, int first_row, int num
 {
     load_rows(x, y, first_row, num_rows, num_attributes, input_file_name);
 }
+
+// The inverse of populate_data: "label,f0,...,f{d-1}" per line, each value in the shortest decimal form that
+// stof() reads back to the same fp32 bits (std::to_chars).  The reference has no writer in C++ -- its data
+// files come out of scripts/convert_mnist_to_odd_even.py and convert_adult.py in this layout; this is what
+// hands the SAME synthetic rows to the reference's own programs (bench.py, tools/refgpu_compare.py).
+// Rows are formatted in parallel into per-thread buffers, then written in order.  Returns 0, or -1 on an I/O error.
+extern "C" int dpsvm_host_write_csv(const char* path, const float* x, const int* y, int n, int d)
+{
+    if (!path || !x || !y || n < 0 || d < 0) return -1;
+    FILE* fp = fopen(path, "wb");
+    if (!fp) return -1;
+    const int threads = std::max(1, std::min<int>({(int)std::thread::hardware_concurrency(), 16, n / 256 + 1}));
+    const int block = 4096;                       // rows per round and thread
+    std::vector<std::string> bufs((size_t)threads);
+    int rc = 0;
+    for (int base = 0; base < n && rc == 0; base += block * threads) {
+        auto work = [&](int t) {
+            std::string& b = bufs[(size_t)t];
+            b.clear();
+            const int lo = std::min(n, base + t * block), hi = std::min(n, lo + block);
+            char tmp[64];
+            for (int i = lo; i < hi; ++i) {
+                auto r = std::to_chars(tmp, tmp + sizeof(tmp), y[i]);
+                b.append(tmp, r.ptr);
+                const float* row = x + (size_t)i * d;
+                for (int k = 0; k < d; ++k) {
+                    b.push_back(',');
+                    if (row[k] == 0.0f && !std::signbit(row[k])) { b.push_back('0'); continue; }
+                    r = std::to_chars(tmp, tmp + sizeof(tmp), row[k]);
+                    b.append(tmp, r.ptr);
+                }
+                b.push_back('\n');
+            }
+        };
+        if (threads == 1) work(0);
+        else {
+            std::vector<std::thread> pool;
+            for (int t = 0; t < threads; ++t) pool.emplace_back(work, t);
+            for (auto& th : pool) th.join();
+        }
+        for (int t = 0; t < threads && rc == 0; ++t)
+            if (!bufs[(size_t)t].empty() && fwrite(bufs[(size_t)t].data(), 1, bufs[(size_t)t].size(), fp) != bufs[(size_t)t].size()) rc = -1;
+    }
+    if (fclose(fp) != 0) rc = -1;
+    return rc;
+}

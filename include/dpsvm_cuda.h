@@ -14,6 +14,12 @@
  *   - stream arguments are cudaStream_t passed as void* (NULL = legacy default stream).
  *   - X is row-major fp32 with a row pitch (in floats) that is a multiple of 4, padding zero-filled
  *     (dpsvm_pitch_for()); labels are int32 +1/-1; indices are int32 GLOBAL row numbers.
+ *   - device pointers to X rows (d_x, d_x_hi, d_x_lo) must be 16-byte aligned: rows are read as 128-bit words and
+ *     staged by TMA bulk copies.  A misaligned pointer is rejected with DPSVM_ERR_INVALID.
+ *   - an EMPTY selection key (an I-set with no member) stands for the reference's default "index 0, +-1e9"
+ *     (svmTrainMain.cpp:249-252).  Where the rows a call holds start at a global index > 0 (index_base, or a
+ *     trainer created with DPSVM_FLAG_X_SHARD_ONLY and shard_start > 0 on a single GPU), the first row held
+ *     stands in for row 0.
  *   - there is no CPU fallback: without a usable CUDA device every compute entry point returns
  *     DPSVM_ERR_CUDA.
  */

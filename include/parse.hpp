@@ -18,4 +18,8 @@ extern void populate_data(std::vector<float> &x, std::vector<int> &y, int num_tr
 extern void populate_data_rows(std::vector<float> &x, std::vector<int> &y, int first_row, int num_rows,
                                int num_attributes, const char* input_file_name);
 
+// The inverse: writes n rows in the layout populate_data reads (the layout the reference's converters produce,
+// scripts/convert_mnist_to_odd_even.py:24-26, convert_adult.py:24-31); values round-trip bit for bit.  0 or -1.
+extern "C" int dpsvm_host_write_csv(const char* path, const float* x, const int* y, int n, int d);
+
 #endif

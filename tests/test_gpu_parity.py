@@ -283,6 +283,67 @@ def test_eta_zero_duplicates(golden, layout):
         assert abs(w_ours - w_seq) < 2e-2 * abs(w_seq), (w_ours, w_seq)
 
 
+@pytest.mark.parametrize("label", [1, -1])
+@pytest.mark.parametrize("chunk", ["128", "2"])
+@pytest.mark.parametrize("loop_flags", [0, capi.FLAG_GRAPH_LOOP])
+def test_training_into_an_empty_set(oracle, monkeypatch, layout, label, chunk, loop_flags):
+    """Rows of one class: I_low (or I_up) has no member, the reference falls back to "index 0, +-1e9"
+    (svmTrainMain.cpp:249-252), applies that update and stops (do-while).  Both loops, two chunk sizes, against the
+    oracle; then the same rows as a shard that starts at global row 500 of a larger set on ONE GPU, where global row 0
+    is not resident and the first resident row stands in for it."""
+    monkeypatch.setenv("DPSVM_CHUNK", chunk)
+    rng = np.random.default_rng(11)
+    n, d = 300, 40
+    x = (rng.random((n, d), dtype=np.float32) < 0.5).astype(np.float32) * rng.random((n, d), dtype=np.float32)
+    y = np.full(n, label, np.int32)
+    ref = oracle.train(x, y, 3.0, 0.2, 1e-3, 1000, kernel_form=1, select_rule=1, trace_cap=8)
+    with capi.Trainer(n, d, 3.0, 0.2, 1e-3, cache_size=4, flags=loop_flags) as t:
+        t.upload(x, y)
+        st = t.train()
+        alpha, f, _ = t.download()
+    assert st.num_iter == ref.num_iter == 1 and st.converged == 1
+    assert (st.i_hi, st.i_lo) == tuple(ref.trace_idx[0]) == (0, 0)
+    assert np.array_equal(alpha, ref.alpha) and np.abs(f - ref.f).max() < F_TOL
+    with capi.Trainer(2000, d, 3.0, 0.2, 1e-3, cache_size=4, shard_rows=n, shard_start=500,
+                      flags=loop_flags | capi.FLAG_X_SHARD_ONLY) as t:
+        t.upload(x, y)
+        st2 = t.train()
+        alpha2, f2, _ = t.download()
+    assert st2.num_iter == 1 and st2.converged == 1 and (st2.i_hi, st2.i_lo) == (500, 500)
+    assert np.array_equal(alpha2, alpha) and np.array_equal(f2, f)
+
+
+def test_resident_launch_refusal_falls_back_to_the_graph_loop(golden, monkeypatch, layout):
+    """A cooperative launch can be refused at run time (MPS/MIG, a grid that is not co-resident).  The trainer then
+    carries on with the graph loop, whose results are bit-identical.  DPSVM_FAULT_RESIDENT_LAUNCH injects the refusal."""
+    g = golden("mnist_512")
+    with _trainer(g, cache_size=4) as t:
+        st0 = t.train()
+        a0, f0, _ = t.download()
+    monkeypatch.setenv("DPSVM_FAULT_RESIDENT_LAUNCH", "1")
+    with _trainer(g, cache_size=4) as t:
+        assert t.loop_info()[0] is True
+        st1 = t.train()
+        assert t.loop_info()[0] is False
+        a1, f1, _ = t.download()
+    assert st0.num_iter == st1.num_iter and st1.converged == 1 and np.array_equal(a0, a1) and np.array_equal(f0, f1)
+
+
+def test_misaligned_row_pointers_are_rejected(torch):
+    z = torch.zeros(256, dtype=torch.float32, device="cuda")
+    k = torch.full((2,), -1, dtype=torch.int64, device="cuda")
+    with pytest.raises(capi.DpsvmError) as e:
+        capi.row_norms(z.data_ptr() + 4, 4, 8, 8, z)
+    assert e.value.code == -1
+    for bad in ("d_x", "d_x_hi", "d_x_lo"):
+        kw = dict(d_x=z.data_ptr(), d_x_hi=z.data_ptr(), d_x_lo=z.data_ptr())
+        kw[bad] = z.data_ptr() + 8
+        with pytest.raises(capi.DpsvmError) as e:
+            capi.smo_pass(n=4, d=8, pitch=8, d_xsq=z, d_y=k, d_alpha=z, d_f=z, xsq_hi=0.0, xsq_lo=0.0, delta_hi=0.0,
+                          delta_lo=0.0, gamma=0.1, c=1.0, index_base=0, d_keys=k, d_line_hi=None, d_line_lo=None, variant=0, **kw)
+        assert e.value.code == -1 and "16-byte" in str(e.value)
+
+
 def test_max_iter_and_chunked_resume(golden, layout):
     g = golden("mnist_512")
     with _trainer(g, max_iter=137) as t:
