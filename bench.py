@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pass-only", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-mirror", action="store_true", help="N>1: keep only the owned rows of X on each GPU (candidate rows then travel in the exchange)")
     ap.add_argument("--no-n1", action="store_true", help="N>1: skip the single-GPU run of the same workload on rank 0")
     return ap.parse_args()
 
@@ -288,13 +289,18 @@ def main():
     ips = args.iters_per_step
     max_iter = 2 ** 31 - 2
 
+    # each rank uploads only its rows; the ranks then mirror one another's rows device to device when that fits easily
+    # (every BASELINE config does: at most 3.1 GB), so the selected pair's rows are local on every GPU
+    mirror = world > 1 and not args.no_mirror and 4.0 * n_total * capi.pitch_for(d) <= 40e9
+
     def make_trainer(extra_flags=0, single=False):
         """A trainer for this rank's shard (joined to the other ranks), or -- single -- for the whole set on this GPU."""
         if single or world == 1:
             return capi.Trainer(n_total, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=max_iter, cache_size=args.cache_size,
                                 device=local_rank, flags=extra_flags)
         t = capi.Trainer(n_total, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=max_iter, cache_size=args.cache_size,
-                         shard_rows=n_shard, shard_start=row0, device=local_rank, flags=capi.FLAG_X_SHARD_ONLY | extra_flags)
+                         shard_rows=n_shard, shard_start=row0, device=local_rank,
+                         flags=capi.FLAG_X_SHARD_ONLY | (capi.FLAG_X_MIRROR if mirror else 0) | extra_flags)
         ids = [capi.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         t.comm_init(ids[0], rank, world)
@@ -574,6 +580,8 @@ def main():
             "iters_per_step": ips, "iterations_timed": done_iters, "converged_during_timing": bool(st.converged),
             "cache_hits": int(st.cache_hits), "cache_lookups": int(st.cache_lookups),
             "rows_per_gpu": n_shard, "us_per_iteration": 1e3 * iter_ms, "exchange": tr.comm_transport,
+            "x_residency": ("each GPU sweeps its own %d rows and holds a read-only mirror of the other ranks' rows (%.2f GB in all) for the pair fetch"
+                            % (n_shard, 4e-9 * n_total * capi.pitch_for(d))) if mirror else ("owned rows only" if world > 1 else "whole set"),
             "loop": "resident (persistent cooperative kernel, %d iterations per launch)" % chunk if resident
                     else "CUDA graph of [control, pass] x %d" % chunk,
             "pass_kernel_alone_us": (1e3 * pass_ms) if pass_ms is not None else None,

@@ -20,6 +20,7 @@ FLAG_X_SHARD_ONLY = 2
 FLAG_GRAPH_LOOP = 4
 FLAG_DENSE = 8
 FLAG_SPARSE = 16
+FLAG_X_MIRROR = 32
 KEY_EMPTY = 0xFFFFFFFFFFFFFFFF
 COMM_ID_BYTES = 128
 
@@ -357,7 +358,7 @@ class Trainer:
 
     @property
     def comm_transport(self) -> str:
-        return {0: "none", 1: "nccl", 2: "p2p"}[lib().dpsvm_comm_transport(self._h)]
+        return {0: "none", 1: "nccl", 2: "p2p", 3: "p2p-ll"}[lib().dpsvm_comm_transport(self._h)]
 
 
 def comm_unique_id() -> bytes:

@@ -41,6 +41,9 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -62,14 +65,19 @@ int load_nccl()
     a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(h, "ncclCommInitRank"));
     a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
     a.AllGather = reinterpret_cast<decltype(a.AllGather)>(dlsym(h, "ncclAllGather"));
+    a.Broadcast = reinterpret_cast<decltype(a.Broadcast)>(dlsym(h, "ncclBroadcast"));
+    a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(dlsym(h, "ncclGroupStart"));
+    a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(dlsym(h, "ncclGroupEnd"));
     a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
-    if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.GetErrorString)
+    if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.Broadcast || !a.GroupStart || !a.GroupEnd || !a.GetErrorString)
         return fail(DPSVM_ERR_COMM, "NCCL library lacks a required symbol");
     g_nccl = a;
     return DPSVM_OK;
 }
 
 constexpr size_t kFlagBytes = 1024;      // flags [2][world] u32 at the head of the mailbox allocation
+// then the flagged-word inbox (kLLBytes, see LLDev), then the mailbox proper [2][world][package]
+constexpr size_t kMailOffset = kFlagBytes + kLLBytes;
 
 struct CommState {
     ncclComm_t comm = nullptr;
@@ -79,9 +87,13 @@ struct CommState {
     unsigned char* d_recv = nullptr;     // world packages
     // p2p transport
     bool p2p = false;
-    unsigned char* d_box = nullptr;      // [kFlagBytes flags][2][world][package]
+    unsigned char* d_box = nullptr;      // [kFlagBytes flags][kLLBytes flagged words][2][world][package]
+    bool ll = false;                     // X mirrored on every rank: candidates travel as flagged words, no rows
+    bool mirrored = false;               // the peers' rows of the current upload have been copied in
+    std::vector<int> shard_start, shard_rows;   // every rank's owned range (all-gathered at init)
     unsigned int* d_counter = nullptr;
     PushDev* d_push = nullptr;
+    PushDev h_push{};                    // host copy of *d_push
     void* opened[kMaxPeers] = {};
     unsigned char* d_tmp = nullptr;      // bootstrap all-gather buffer
 };
@@ -109,7 +121,7 @@ int try_setup_p2p(dpsvm_ctx* c, CommState* s)
 {
     const int world = c->world;
     if (world > kMaxPeers) return 0;
-    const size_t box_bytes = kFlagBytes + 2 * (size_t)world * s->package;
+    const size_t box_bytes = kMailOffset + 2 * (size_t)world * s->package;
     // every rank performs the same collective calls whatever happens locally (a local failure only
     // turns this rank's vote into 0)
     int ok = 1;
@@ -142,6 +154,8 @@ int try_setup_p2p(dpsvm_ctx* c, CommState* s)
     h.world = world;
     h.rank = c->rank;
     h.package = s->package;
+    h.timeout_ns = c->timeout_ns;
+    const bool mirror = (c->p.flags & DPSVM_FLAG_X_MIRROR) != 0;
     for (int q = 0; q < world && ok; ++q) {
         unsigned char* base = nullptr;
         if (q == c->rank) {
@@ -157,8 +171,11 @@ int try_setup_p2p(dpsvm_ctx* c, CommState* s)
             base = static_cast<unsigned char*>(p);
         }
         h.peer_flag[q] = reinterpret_cast<unsigned int*>(base);
-        h.peer_mail[q] = base + kFlagBytes;
+        h.peer_mail[q] = base + kMailOffset;
+        if (mirror) h.ll.peer_in[q] = reinterpret_cast<unsigned long long*>(base + kFlagBytes);
     }
+    if (mirror && ok) h.ll.in = reinterpret_cast<unsigned long long*>(s->d_box + kFlagBytes);
+    s->h_push = h;
     if (ok && cudaMemcpy(s->d_push, &h, sizeof(h), cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); ok = 0; }
     return ok;
 }
@@ -177,6 +194,30 @@ void comm_free(dpsvm_ctx* c)
     c->d_push = nullptr;
 }
 
+// DPSVM_FLAG_X_MIRROR: after an upload every rank copies the rows the OTHER ranks own -- with the labels and the |x|^2
+// their owners computed (each owner sums in the order of its own sweep) -- device to device over NVLink, one
+// broadcast per owner.  The sweep still reads only the owned shard; the copies exist so that the two rows of the
+// selected pair, whoever owns them, are one local TMA copy away, as on a single GPU.
+int comm_mirror(dpsvm_ctx* c)
+{
+    CommState* s = static_cast<CommState*>(c->comm);
+    if (!s || !s->comm || !(c->p.flags & DPSVM_FLAG_X_MIRROR)) return DPSVM_OK;
+    ncclResult_t r = g_nccl.GroupStart();
+    for (int q = 0; q < c->world && r == 0; ++q) {
+        const size_t row0 = (size_t)(s->shard_start[(size_t)q] - c->res0), rows = (size_t)s->shard_rows[(size_t)q];
+        float* x = c->d_x + row0 * (size_t)c->pitch;
+        r = g_nccl.Broadcast(x, x, rows * (size_t)c->pitch * sizeof(float), ncclChar, q, s->comm, c->stream);
+        if (r == 0) r = g_nccl.Broadcast(c->d_y + row0, c->d_y + row0, rows * sizeof(int), ncclChar, q, s->comm, c->stream);
+        if (r == 0) r = g_nccl.Broadcast(c->d_xsq + row0, c->d_xsq + row0, rows * sizeof(float), ncclChar, q, s->comm, c->stream);
+    }
+    const ncclResult_t r2 = g_nccl.GroupEnd();
+    if (r != 0 || r2 != 0) return fail(DPSVM_ERR_COMM, "mirroring X: %s", g_nccl.GetErrorString(r != 0 ? r : r2));
+    const cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "mirroring X: %s", cudaGetErrorString(e));
+    s->mirrored = true;
+    return DPSVM_OK;
+}
+
 // After the local (re)selection at setup/reset: make the first package available to every rank.
 int comm_after_select(dpsvm_ctx* c)
 {
@@ -184,7 +225,7 @@ int comm_after_select(dpsvm_ctx* c)
     if (!s || !s->p2p) return DPSVM_OK;
     // clear my flags, then a barrier (an all-gather completes only after every rank has contributed,
     // i.e. after every rank's clear is ordered before its contribution), then the initial push
-    cudaError_t e = cudaMemsetAsync(s->d_box, 0, kFlagBytes, c->stream);
+    cudaError_t e = cudaMemsetAsync(s->d_box, 0, kMailOffset, c->stream);      // arrival flags and flagged words
     if (e == cudaSuccess) e = cudaMemsetAsync(s->d_counter, 0, sizeof(unsigned int), c->stream);
     if (e != cudaSuccess) return fail(DPSVM_ERR_CUDA, "comm reset: %s", cudaGetErrorString(e));
     ncclResult_t r = g_nccl.AllGather(s->d_send, s->d_recv, 8, ncclChar, s->comm, c->stream);
@@ -201,8 +242,10 @@ bool comm_fill_resident(dpsvm_ctx* c, ResidentDev* a)
     CommState* s = static_cast<CommState*>(c->comm);
     if (!s || !s->p2p) return false;
     a->world = c->world;
+    a->rank = c->rank;
     a->push = s->d_push;
-    a->mail = s->d_box + kFlagBytes;
+    if (s->ll) a->ll = s->h_push.ll;
+    a->mail = s->d_box + kMailOffset;
     a->flags = reinterpret_cast<const unsigned int*>(s->d_box);
     a->package = s->package;
     return true;
@@ -219,9 +262,11 @@ int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t stream, int variant)
     ctl.own0 = c->p.shard_start;
     ctl.own_n = c->p.shard_rows;
     cudaError_t e;
+    ctl.timeout_ns = c->timeout_ns;
     if (s->p2p) {
-        ctl.cand = s->d_box + kFlagBytes;
+        ctl.cand = s->d_box + kMailOffset;
         ctl.flags = reinterpret_cast<const unsigned int*>(s->d_box);
+        if (s->ll) ctl.ll_in = s->h_push.ll.in;
     } else {
         PackDev p{};
         p.keys = c->d_keys;
@@ -275,7 +320,7 @@ extern "C" int dpsvm_comm_init(dpsvm_ctx* c, const unsigned char id[DPSVM_COMM_I
     if (world == 1) { c->world = 1; c->rank = 0; return DPSVM_OK; }
     if (!(c->p.flags & DPSVM_FLAG_X_SHARD_ONLY))
         return fail(DPSVM_ERR_STATE, "dpsvm_comm_init needs a context created with DPSVM_FLAG_X_SHARD_ONLY "
-                                     "(each rank keeps only its rows; candidates travel in the exchange)");
+                                     "(each rank uploads only its rows; candidates travel in the exchange)");
     int rc = load_nccl();
     if (rc != DPSVM_OK) return rc;
     cudaError_t e = cudaSetDevice(c->device);
@@ -296,25 +341,49 @@ extern "C" int dpsvm_comm_init(dpsvm_ctx* c, const unsigned char id[DPSVM_COMM_I
     c->comm = s;
     c->world = world;
     c->rank = rank;
-    // (the resident loop runs multi-GPU only over the peer-memory exchange; decided below)
 
-    // transport: peer memory unless told otherwise; every rank must agree, so the outcome is voted on
+    // What every rank must agree on is gathered FIRST, by a collective every rank joins whatever its environment
+    // says: the owned row ranges, whether this rank asks for the NCCL transport (DPSVM_EXCHANGE=nccl), its flags.
     const char* ex = getenv("DPSVM_EXCHANGE");
-    int mine = (ex && strcmp(ex, "nccl") == 0) ? 0 : try_setup_p2p(c, s);
+    int mine4[4] = {c->p.shard_start, c->p.shard_rows, (ex && strcmp(ex, "nccl") == 0) ? 1 : 0, c->p.flags & DPSVM_FLAG_X_MIRROR};
+    std::vector<int> all4((size_t)world * 4, 0);
+    rc = nccl_gather_bytes(c, s, mine4, all4.data(), sizeof(mine4));
+    if (rc != DPSVM_OK) return rc;
+    bool any_nccl = false, mirror_all = true, mirror_any = false;
+    s->shard_start.resize((size_t)world);
+    s->shard_rows.resize((size_t)world);
+    for (int q = 0; q < world; ++q) {
+        s->shard_start[(size_t)q] = all4[(size_t)q * 4];
+        s->shard_rows[(size_t)q] = all4[(size_t)q * 4 + 1];
+        any_nccl = any_nccl || all4[(size_t)q * 4 + 2] != 0;
+        mirror_all = mirror_all && all4[(size_t)q * 4 + 3] != 0;
+        mirror_any = mirror_any || all4[(size_t)q * 4 + 3] != 0;
+    }
+    if (mirror_any != mirror_all) return fail(DPSVM_ERR_INVALID, "dpsvm_comm_init: DPSVM_FLAG_X_MIRROR must be set on every rank or on none");
+
+    // transport: peer memory unless any rank asked otherwise; every rank maps its peers (or skips it) alike, and the
+    // outcome is voted on
+    int mine = any_nccl ? 0 : try_setup_p2p(c, s);
     std::vector<int> votes((size_t)world, 0);
     rc = nccl_gather_bytes(c, s, &mine, votes.data(), sizeof(int));
     if (rc != DPSVM_OK) return rc;
     bool all_ok = true;
     for (int v : votes) all_ok = all_ok && v != 0;
     s->p2p = all_ok;
+    s->ll = all_ok && mirror_all;
     c->d_push = all_ok ? s->d_push : nullptr;
     c->exchange_p2p = all_ok ? 1 : 0;
-    if (c->uploaded) return comm_after_select(c);
+    if (c->uploaded) {
+        rc = comm_mirror(c);
+        if (rc != DPSVM_OK) return rc;
+        return comm_after_select(c);
+    }
     return DPSVM_OK;
 }
 
 extern "C" int dpsvm_comm_transport(dpsvm_ctx* c)
 {
     if (!c || c->world <= 1 || !c->comm) return 0;
-    return c->exchange_p2p ? 2 : 1;
+    if (!c->exchange_p2p) return 1;
+    return static_cast<CommState*>(c->comm)->ll ? 3 : 2;
 }

@@ -106,6 +106,7 @@ CtlDev make_ctl_args(dpsvm_ctx* c)
     a.max_iter = c->p.max_iter;
     a.cache = c->cache;
     a.pdl = c->pdl;
+    a.timeout_ns = c->timeout_ns;
     return a;
 }
 
@@ -207,6 +208,7 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.lru_meta = c->d_lru + 2 * kResCacheLines;
     a.sp = c->sp;
     a.world = 1;
+    a.timeout_ns = c->timeout_ns;
     if (c->world > 1 && !comm_fill_resident(c, &a)) return fail(DPSVM_ERR_STATE, "resident loop needs the peer-memory exchange");
     const int trace_on = env_int("DPSVM_TRACE", 0);
     if (trace_on && !c->d_trace) { CU(cudaMalloc(&c->d_trace, sizeof(unsigned long long) * 8 * 1024)); CU(cudaMemset(c->d_trace, 0, sizeof(unsigned long long) * 8 * 1024)); }
@@ -428,8 +430,18 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     cudaGetDevice(&c->device);
     c->pitch = dpsvm_pitch_for(p->num_attributes);
     const bool shard_only = (p->flags & DPSVM_FLAG_X_SHARD_ONLY) != 0;
-    c->res0 = shard_only ? p->shard_start : 0;
-    c->res_n = shard_only ? p->shard_rows : p->num_train_data;
+    if ((p->flags & DPSVM_FLAG_X_MIRROR) && !shard_only) {
+        delete c;
+        return fail(DPSVM_ERR_INVALID, "dpsvm_create: DPSVM_FLAG_X_MIRROR goes with DPSVM_FLAG_X_SHARD_ONLY (the upload brings the owned rows, the peers bring the rest)");
+    }
+    // rows resident on this GPU: everything (reference layout, or the owned rows plus a mirror of the peers'), or the shard
+    const bool keep_shard_only = shard_only && !(p->flags & DPSVM_FLAG_X_MIRROR);
+    c->res0 = keep_shard_only ? p->shard_start : 0;
+    c->res_n = keep_shard_only ? p->shard_rows : p->num_train_data;
+    {
+        const int ms = env_int("DPSVM_TIMEOUT_MS", 10000);
+        c->timeout_ns = (unsigned long long)(ms > 0 ? ms : 10000) * 1000000ull;
+    }
     c->chunk = env_int("DPSVM_CHUNK", 128);
     if (c->chunk < 1) c->chunk = 1;
     c->variant = env_int("DPSVM_VARIANT", dpsvm_pass_variant(p->shard_rows, c->pitch, 0));
@@ -518,7 +530,20 @@ static int finish_upload(dpsvm_ctx* c)
         c->variant = mb > 64.0 ? (2 | (pin_mb << 8)) : 0;
     }
     c->uploaded = true;
+    if (c->comm) {                  // DPSVM_FLAG_X_MIRROR: the peers' rows, labels and |x|^2 (collective; a no-op otherwise)
+        rc = comm_mirror(c);
+        if (rc != DPSVM_OK) return rc;
+    }
     return reset_state(c);
+}
+
+// Rows an upload brings: all resident rows (reference layout) or the owned shard only (DPSVM_FLAG_X_SHARD_ONLY; with
+// DPSVM_FLAG_X_MIRROR the other ranks' rows then arrive device to device).
+static void upload_range(const dpsvm_ctx* c, size_t* first_row, size_t* rows)
+{
+    const bool shard_only = (c->p.flags & DPSVM_FLAG_X_SHARD_ONLY) != 0;
+    *first_row = shard_only ? (size_t)(c->p.shard_start - c->res0) : 0;
+    *rows = shard_only ? (size_t)c->p.shard_rows : (size_t)c->res_n;
 }
 
 int dpsvm_upload(dpsvm_ctx* c, const float* h_x, const int32_t* h_y)
@@ -526,14 +551,17 @@ int dpsvm_upload(dpsvm_ctx* c, const float* h_x, const int32_t* h_y)
     if (!c || !h_x || !h_y) return fail(DPSVM_ERR_INVALID, "dpsvm_upload: null argument");
     CU(cudaSetDevice(c->device));
     const int d = c->p.num_attributes;
+    size_t row0, rows;
+    upload_range(c, &row0, &rows);
+    float* dst = c->d_x + row0 * (size_t)c->pitch;
     if (c->pitch != d) {
-        CU(cudaMemsetAsync(c->d_x, 0, sizeof(float) * (size_t)c->res_n * c->pitch, c->stream));
-        CU(cudaMemcpy2DAsync(c->d_x, sizeof(float) * (size_t)c->pitch, h_x, sizeof(float) * (size_t)d, sizeof(float) * (size_t)d,
-                             (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemsetAsync(dst, 0, sizeof(float) * rows * c->pitch, c->stream));
+        CU(cudaMemcpy2DAsync(dst, sizeof(float) * (size_t)c->pitch, h_x, sizeof(float) * (size_t)d, sizeof(float) * (size_t)d,
+                             rows, cudaMemcpyHostToDevice, c->stream));
     } else {
-        CU(cudaMemcpyAsync(c->d_x, h_x, sizeof(float) * (size_t)c->res_n * d, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(dst, h_x, sizeof(float) * rows * d, cudaMemcpyHostToDevice, c->stream));
     }
-    CU(cudaMemcpyAsync(c->d_y, h_y, sizeof(int) * (size_t)c->res_n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_y + row0, h_y, sizeof(int) * rows, cudaMemcpyHostToDevice, c->stream));
     return finish_upload(c);
 }
 
@@ -544,8 +572,10 @@ int dpsvm_upload_device(dpsvm_ctx* c, const float* d_x_shard, int pitch, const i
         return fail(DPSVM_ERR_STATE, "dpsvm_upload_device needs DPSVM_FLAG_X_SHARD_ONLY (or a single shard)");
     if (pitch != c->pitch) return fail(DPSVM_ERR_INVALID, "dpsvm_upload_device: pitch %d, expected %d", pitch, c->pitch);
     CU(cudaSetDevice(c->device));
-    CU(cudaMemcpyAsync(c->d_x, d_x_shard, sizeof(float) * (size_t)c->res_n * c->pitch, cudaMemcpyDeviceToDevice, c->stream));
-    CU(cudaMemcpyAsync(c->d_y, d_y_shard, sizeof(int) * (size_t)c->res_n, cudaMemcpyDeviceToDevice, c->stream));
+    size_t row0, rows;
+    upload_range(c, &row0, &rows);
+    CU(cudaMemcpyAsync(c->d_x + row0 * (size_t)c->pitch, d_x_shard, sizeof(float) * rows * c->pitch, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_y + row0, d_y_shard, sizeof(int) * rows, cudaMemcpyDeviceToDevice, c->stream));
     return finish_upload(c);
 }
 

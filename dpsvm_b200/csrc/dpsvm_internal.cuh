@@ -65,6 +65,7 @@ struct dpsvm_ctx {
     void* comm = nullptr;        // opaque (comm.cu)
     const dpsvm::PushDev* d_push = nullptr;   // peer-memory exchange descriptor (device), null otherwise
     int exchange_p2p = 0;
+    unsigned long long timeout_ns = 10000000000ull;   // bound of every device-side wait for other CTAs / ranks (DPSVM_TIMEOUT_MS)
 
     // predict scratch (predict.cu)
     void* predict = nullptr;
@@ -87,6 +88,7 @@ void predict_free(dpsvm_ctx* c);
 void comm_free(dpsvm_ctx* c);
 int comm_launch_iteration(dpsvm_ctx* c, cudaStream_t s, int variant);
 int comm_after_select(dpsvm_ctx* c);
+int comm_mirror(dpsvm_ctx* c);        // DPSVM_FLAG_X_MIRROR: copy the other ranks' rows, labels and |x|^2 in (collective)
 bool comm_fill_resident(dpsvm_ctx* c, ResidentDev* a);   // false: this exchange cannot run inside the resident loop
 
 }  // namespace dpsvm

@@ -66,6 +66,84 @@ __device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p
     return v;
 }
 
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Flagged-word candidate exchange (LLDev, smo_kernels.cuh).  8-byte stores are single-copy atomic, and each word
+// names the package it belongs to, so neither side needs a fence: the receiver spins on the words themselves.
+// ------------------------------------------------------------------------------------------------
+// data word `w` (0..5) of a rank's candidates
+__device__ __forceinline__ unsigned int ll_word(int w, unsigned long long k_up, float a_up, unsigned long long k_low, float a_low)
+{
+    switch (w) {
+        case 0: return (unsigned int)(k_up >> 32);
+        case 1: return (unsigned int)k_up;
+        case 2: return __float_as_uint(a_up);
+        case 3: return (unsigned int)(k_low >> 32);
+        case 4: return (unsigned int)k_low;
+        default: return __float_as_uint(a_low);
+    }
+}
+// store word `w` of package `seq` from rank `rank` into rank q's inbox
+__device__ __forceinline__ void ll_send(const LLDev& ll, int q, int rank, unsigned int seq, int w, unsigned int data)
+{
+    unsigned long long* dst = ll.peer_in[q] + ((size_t)(seq & 1u) * kMaxPeers + rank) * kLLWords + w;
+    st_relaxed_sys_u64(dst, ((unsigned long long)(seq + 1u) << 32) | data);
+}
+// Wait for package `seq` of every rank (threads tid < world * 8 take one word each and leave its data in
+// s_ll[tid]); *s_ok is cleared on timeout.  Block-wide: contains two barriers.
+__device__ __forceinline__ bool ll_wait(const unsigned long long* in, int world, unsigned int seq, unsigned int* s_ll, int* s_ok,
+                                        unsigned long long timeout_ns)
+{
+    const int tid = threadIdx.x;
+    if (tid == 0) *s_ok = 1;
+    __syncthreads();
+    if (tid < world * kLLWords && (tid & (kLLWords - 1)) < 6) {
+        const unsigned long long* w = in + (size_t)(seq & 1u) * kMaxPeers * kLLWords + tid;
+        const unsigned int want = seq + 1u;
+        unsigned long long v = ld_relaxed_sys_u64(w);
+        if ((unsigned int)(v >> 32) != want) {
+            const unsigned long long t0 = global_timer_ns();
+            unsigned int spins = 0;
+            while ((unsigned int)((v = ld_relaxed_sys_u64(w)) >> 32) != want) {
+                if ((++spins & 0xFFu) == 0 && global_timer_ns() - t0 > timeout_ns) { *s_ok = 0; break; }
+            }
+        }
+        s_ll[tid] = (unsigned int)v;
+    }
+    __syncthreads();
+    return *s_ok != 0;
+}
+// Global merge of the gathered candidates (svmTrainMain.cpp:255-274): minimum packed key = argmin f / argmax f with
+// the lowest GLOBAL index among equal values; with every set empty the defaults are rank 0's (its first row is row 0).
+__device__ __forceinline__ void ll_merge(const unsigned int* s_ll, int world, unsigned long long& g_up, float& a_up,
+                                         unsigned long long& g_low, float& a_low)
+{
+    g_up = DPSVM_KEY_EMPTY; g_low = DPSVM_KEY_EMPTY;
+    a_up = __uint_as_float(s_ll[2]); a_low = __uint_as_float(s_ll[5]);
+    for (int r = 0; r < world; ++r) {
+        const unsigned int* p = s_ll + r * kLLWords;
+        const unsigned long long u = ((unsigned long long)p[0] << 32) | p[1], l = ((unsigned long long)p[3] << 32) | p[4];
+        if (u < g_up) { g_up = u; a_up = __uint_as_float(p[2]); }
+        if (l < g_low) { g_low = l; a_low = __uint_as_float(p[5]); }
+    }
+}
+
 template <bool HINT>
 __device__ __forceinline__ float4 ldg_x4(const float4* p, uint64_t pol)
 {
@@ -280,6 +358,20 @@ __device__ __forceinline__ void push_package(const PushDev& p, unsigned long lon
     const int tid = threadIdx.x, nthr = blockDim.x;
     const unsigned int slot = seq & 1u;
     float f_dummy;
+    if (p.ll.in) {
+        // every rank holds all of X: only keys and alphas travel, as flagged words (one thread per word and peer)
+        if (tid < p.world * kLLWords && (tid & (kLLWords - 1)) < 6) {
+            int i_up = p.own0, i_low = p.own0;          // empty set: the alpha of the first owned row (rank 0: global row 0)
+            if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_up);
+            if (k_low != DPSVM_KEY_EMPTY) unpack_key_low(k_low, &f_dummy, &i_low);
+            const int w = tid & (kLLWords - 1);
+            float au = a_up, al = a_low;
+            if (w == 2 && !(have_alpha && k_up != DPSVM_KEY_EMPTY)) au = __ldcg(p.alpha + (i_up - p.res0));
+            if (w == 5 && !(have_alpha && k_low != DPSVM_KEY_EMPTY)) al = __ldcg(p.alpha + (i_low - p.res0));
+            ll_send(p.ll, tid / kLLWords, p.rank, seq, w, ll_word(w, k_up, au, k_low, al));
+        }
+        return;
+    }
     int i_hi = p.own0, i_lo = p.own0;      // an empty set still ships a valid row (the first owned one), so that the
                                            // reference's "index 0, +-1e9" default (svmTrainMain.cpp:249-252) stays defined
     if (k_up != DPSVM_KEY_EMPTY) unpack_key_up(k_up, &f_dummy, &i_hi);

@@ -565,8 +565,26 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
     float b_hi, b_lo;
     const CandHeader* h_hi = nullptr;
     const CandHeader* h_lo = nullptr;
+    bool ll_alpha = false;
+    float ll_a_hi = 0.f, ll_a_lo = 0.f;
     if (a.directed) {
         i_hi = a.dir_i_hi; i_lo = a.dir_i_lo; b_hi = 0.f; b_lo = 0.f;
+    } else if (a.world > 1 && a.ll_in) {
+        // flagged-word exchange (every rank holds all of X): keys and alphas of every rank's candidates; the rows, y
+        // and |x|^2 of the pair are read from local memory below, exactly as on one GPU
+        __shared__ unsigned int s_ll[kMaxPeers * kLLWords];
+        __shared__ int s_ok;
+        if (!ll_wait(a.ll_in, a.world, (unsigned int)num_iter, s_ll, &s_ok, a.timeout_ns)) {
+            if (tid == 0) { st->error = 1; st->done = 1; st->pass.active = 0; }
+            return;
+        }
+        unsigned long long g_up, g_low;
+        ll_merge(s_ll, a.world, g_up, ll_a_hi, g_low, ll_a_lo);
+        ll_alpha = true;
+        unpack_key_up(g_up, &b_hi, &i_hi);
+        unpack_key_low(g_low, &b_lo, &i_lo);
+        if (g_up == DPSVM_KEY_EMPTY) i_hi = a.res0;
+        if (g_low == DPSVM_KEY_EMPTY) i_lo = a.res0;
     } else if (a.world > 1) {
         const unsigned char* cand = a.cand + (a.flags ? (size_t)(num_iter & 1) * a.world * a.cand_stride : 0);
         if (a.flags) {
@@ -584,7 +602,7 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
                 while (ld_acquire_sys_u32(fl) != want) {
                     unsigned long long t1;
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                    if (t1 - t0 > 4000000000ull) { s_timeout = 1; break; }     // 4 s
+                    if (t1 - t0 > a.timeout_ns) { s_timeout = 1; break; }
                     __nanosleep(64);
                 }
             }
@@ -632,8 +650,8 @@ __global__ void __launch_bounds__(kCtlThreads, 1) smo_control_kernel(const CtlDe
         switch (tid) {
             case 0: v = h_hi ? (float)h_hi->y_hi : (float)a.y[r_hi]; break;
             case 1: v = h_lo ? (float)h_lo->y_lo : (float)a.y[r_lo]; break;
-            case 2: v = h_hi ? h_hi->a_hi : a.alpha[r_hi]; break;
-            case 3: v = h_lo ? h_lo->a_lo : a.alpha[r_lo]; break;
+            case 2: v = ll_alpha ? ll_a_hi : (h_hi ? h_hi->a_hi : a.alpha[r_hi]); break;
+            case 3: v = ll_alpha ? ll_a_lo : (h_lo ? h_lo->a_lo : a.alpha[r_lo]); break;
             case 4: v = h_hi ? h_hi->xsq_hi : a.xsq[r_hi]; break;
             case 5: v = h_lo ? h_lo->xsq_lo : a.xsq[r_lo]; break;
             case 6: v = cache_on ? __int_as_float(a.cache.line_of_key[i_hi]) : 0.f; break;

@@ -118,6 +118,19 @@ struct PackDev {
 // memory), fences, and raises its flag there to seq + 1; the next control kernel waits for all
 // `world` flags of that slot.  seq = DevState::num_iter, which every rank advances identically.
 constexpr int kMaxPeers = 16;
+
+// Flagged-word exchange ("LL": every 8-byte word carries 4 bytes of data and the sequence number it belongs to, so
+// a word is valid the moment it is seen -- no fence, no separate flag, ONE one-way trip over NVLink).  Used when
+// every rank holds all of X (DPSVM_FLAG_X_MIRROR): only the candidates travel, 6 words per rank and iteration:
+//   word 0/1/2 = ord(f_up), index_up, alpha_up      word 3/4/5 = ord(-f_low), index_low, alpha_low
+// Inbox of a rank: in[2 parities][kMaxPeers sources][8 words]; package `seq` goes to parity seq & 1 with flag seq + 1.
+constexpr int kLLWords = 8;             // words per (parity, source) slot: 6 used, 64-byte slots
+constexpr size_t kLLBytes = 2 * (size_t)kMaxPeers * kLLWords * sizeof(unsigned long long);
+struct LLDev {
+    unsigned long long* in;                     // this rank's inbox (null: the flagged-word exchange is not in use)
+    unsigned long long* peer_in[kMaxPeers];     // rank q's inbox as mapped here (q == rank: local)
+};
+
 struct PushDev {
     unsigned int* counter;          // CTAs of the current pass that have finished
     unsigned long long* keys;       // [2] local selection; reset to empty after packing
@@ -132,6 +145,8 @@ struct PushDev {
     size_t package;                 // bytes per package
     unsigned char* peer_mail[kMaxPeers];   // base of rank q's mailbox as mapped here (q == rank: local)
     unsigned int* peer_flag[kMaxPeers];
+    LLDev ll;                       // ll.in != null: candidates travel as flagged words, rows come from the local mirror of X
+    unsigned long long timeout_ns;
 };
 
 struct CtlDev {
@@ -159,6 +174,8 @@ struct CtlDev {
     const unsigned int* flags;  // peer-memory exchange: [2 slots][world] arrival flags (null: cand is already complete)
     const float* ext_row_hi;    // optional externally supplied rows (device pointers)
     const float* ext_row_lo;
+    const unsigned long long* ll_in;   // flagged-word exchange: this rank's inbox (rows, y, |x|^2 then come from the local mirror)
+    unsigned long long timeout_ns;     // bound of the wait for the peers' candidates
 };
 
 // ---- resident loop (smo_resident.cu): persistent cooperative kernel, one CTA per SM ----
@@ -200,11 +217,13 @@ struct ResidentDev {
     int stream_evict_first;
     int parity0;                // sweep direction of the launch's first iteration
     // multi-GPU (world > 1): the pair comes from the peer-memory mailbox (see PushDev); CTA 0 publishes
-    int world;
+    int world, rank;
     const PushDev* push;
     const unsigned char* mail;  // local mailbox [2][world][package]
     const unsigned int* flags;  // local arrival flags [2][world]
     size_t package;
+    LLDev ll;                   // ll.in != null: flagged-word exchange (X mirrored on every rank)
+    unsigned long long timeout_ns;   // bound of every spin (grid barrier, peers' candidates)
     unsigned long long* trace;  // optional [grid][4] globaltimer stamps of iteration trace_iter (DPSVM_TRACE)
     int trace_iter;
     SparseDev sp;               // sp.val != null: sweep the sparse stream instead of x4

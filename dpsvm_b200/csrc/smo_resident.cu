@@ -46,7 +46,7 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p
 }
 
 // All CTAs of the (co-resident) grid arrive; returns false on timeout.
-__device__ __forceinline__ bool grid_barrier(unsigned int* counter, unsigned int target, int* s_flag)
+__device__ __forceinline__ bool grid_barrier(unsigned int* counter, unsigned int target, int* s_flag, unsigned long long timeout_ns)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -62,7 +62,7 @@ __device__ __forceinline__ bool grid_barrier(unsigned int* counter, unsigned int
             if ((++spins & 0x3FFu) == 0) {
                 unsigned long long t1;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                if (t1 - t0 > 4000000000ull) { ok = 0; break; }      // 4 s: something is badly wrong
+                if (t1 - t0 > timeout_ns) { ok = 0; break; }      // seconds: something is badly wrong
             }
         }
         *s_flag = ok;
@@ -157,6 +157,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     __shared__ int s_flag;
     __shared__ int s_lru_key[kResCacheLines], s_lru_stamp[kResCacheLines], s_lru_meta[2];
     __shared__ PassScalars s_ps;
+    __shared__ unsigned int s_ll[kMaxPeers * kLLWords];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sub = SPARSE ? lane % SGL : lane % LPR, grp = SPARSE ? lane / SGL : lane / LPR;
@@ -205,7 +206,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 if ((++spins & 0xFFu) == 0) {
                     unsigned long long t1;
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                    if (t1 - t0 > 4000000000ull) { s_flag = 0; break; }
+                    if (t1 - t0 > a.timeout_ns) { s_flag = 0; break; }
                 }
             }
         }
@@ -231,6 +232,21 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         m_src_lo = reinterpret_cast<const float4*>(h_lo + 1) + a.pitch4;
         return true;
     };
+
+    // Same, when every rank holds all of X (flagged-word exchange): only keys and alphas arrive; the rows, y and |x|^2 of
+    // the pair are then read from local memory exactly as on one GPU.
+    const bool ll_mode = a.world > 1 && a.ll.in != nullptr;
+    auto acquire_ll = [&](unsigned int seq) -> bool {
+        if (!ll_wait(a.ll.in, a.world, seq, s_ll, &s_flag, a.timeout_ns)) return false;
+        unsigned long long g_up, g_low;
+        ll_merge(s_ll, a.world, g_up, a_hi_old, g_low, a_lo_old);
+        unpack_key_up(g_up, &b_hi, &i_hi);
+        unpack_key_low(g_low, &b_lo, &i_lo);
+        if (g_up == DPSVM_KEY_EMPTY) i_hi = a.empty_row;
+        if (g_low == DPSVM_KEY_EMPTY) i_lo = a.empty_row;
+        return true;
+    };
+    auto acquire = [&](unsigned int seq) -> bool { return ll_mode ? acquire_ll(seq) : acquire_remote(seq); };
 
     if (a.world <= 1) {
         // the selection left in the global keys by setup / the previous launch
@@ -285,9 +301,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     if (tid == 0) mbar_init(&s_bar, 1);
     unsigned int bar_target = (unsigned int)G;
     // everyone has read alpha of the initial pair before any owner overwrites it
-    if (!grid_barrier(a.barrier, bar_target, &s_flag)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
+    if (!grid_barrier(a.barrier, bar_target, &s_flag, a.timeout_ns)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
     bar_target += (unsigned int)G;
-    if (a.world > 1 && !acquire_remote((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
+    if (a.world > 1 && !acquire((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
 
     uint64_t pol_keep, pol_stream;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
@@ -354,7 +370,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const int r_hi = i_hi - a.index_base, r_lo = i_lo - a.index_base;     // may lie outside [0, n) on a multi-GPU run
         int y_hi, y_lo;
         float xsq_hi, xsq_lo;
-        if (a.world > 1) {
+        if (a.world > 1 && !ll_mode) {
             // rows travelled in the packages (written by peers over NVLink): plain L2 loads into smem
             for (int i = tid; i < a.pitch4; i += kResThreads) { s_hi[i] = __ldcg(m_src_hi + i); s_lo[i] = __ldcg(m_src_lo + i); }
             y_hi = m_y_hi; y_lo = m_y_lo; xsq_hi = m_xsq_hi; xsq_lo = m_xsq_lo;
@@ -561,7 +577,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         }
         num_iter += 1;
 
-        if (!grid_barrier(a.barrier, bar_target, &s_flag)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
+        if (!grid_barrier(a.barrier, bar_target, &s_flag, a.timeout_ns)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
         bar_target += (unsigned int)G;
         stamp(it, 3);
 
@@ -588,7 +604,20 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         // multi-GPU: CTA 0 publishes this rank's candidates to every rank (also on the last iteration of the
         // launch: the next launch starts by waiting for exactly these packages)
         stamp(it, 4);
-        if (a.world > 1 && cta == 0) push_package(*a.push, nxt_up.key, nxt_low.key, nxt_up.alpha, nxt_low.alpha, true, (unsigned int)num_iter);
+        if (a.world > 1 && cta == 0) {
+            if (ll_mode) {
+                // one 8-byte flagged word per thread and peer, straight from registers: nothing to fence, nothing to read
+                if (tid < a.world * kLLWords && (tid & (kLLWords - 1)) < 6) {
+                    // an empty set ships the alpha of the first owned row (on rank 0 that is global row 0, the default)
+                    const float au = nxt_up.key == DPSVM_KEY_EMPTY ? __ldcg(a.alpha) : nxt_up.alpha;
+                    const float al = nxt_low.key == DPSVM_KEY_EMPTY ? __ldcg(a.alpha) : nxt_low.alpha;
+                    const int w = tid & (kLLWords - 1);
+                    ll_send(a.ll, tid / kLLWords, a.rank, (unsigned int)num_iter, w, ll_word(w, nxt_up.key, au, nxt_low.key, al));
+                }
+            } else {
+                push_package(*a.push, nxt_up.key, nxt_low.key, nxt_up.alpha, nxt_low.alpha, true, (unsigned int)num_iter);
+            }
+        }
         stamp(it, 5);
         if (last_iter) {
             if (cta == 0 && tid == 0) {
@@ -601,7 +630,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             break;
         }
         if (a.world > 1) {
-            if (!acquire_remote((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
+            if (!acquire((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
             stamp(it, 6);
         } else {
             unpack_key_up(nxt_up.key, &b_hi, &i_hi);

@@ -281,10 +281,16 @@ int sparse_setup(dpsvm_ctx* c)
     // auto, drop-in layout with the whole of X on every rank (svmTrain.cu:344) but only a shard owned: |x|^2 of the
     // rows other ranks own would be summed in THIS rank's order, which need not be the owner's (the lane count
     // follows the shard's mean row length).  Keep the one order every rank shares.
-    const bool foreign_rows = c->res_n != n;
+    // (With DPSVM_FLAG_X_MIRROR the other ranks' rows arrive later, device to device, TOGETHER with the |x|^2 their
+    // owners computed: only the owned rows are summed here, and no order is shared.)
+    const bool mirror = (c->p.flags & DPSVM_FLAG_X_MIRROR) != 0;
+    const bool foreign_rows = !mirror && c->res_n != n;
+    auto dense_norms = [&]() -> cudaError_t {
+        return mirror ? launch_row_norms(x_own, n, pitch, c->d_xsq + off, s) : launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s);
+    };
     if (mode == 1 || pitch > kSparseMaxPitch || (mode == 0 && (small || foreign_rows))) {
         if (mode == 2) return fail(DPSVM_ERR_LIMIT, "sparse layout supports rows of at most %d floats (pitch %d)", kSparseMaxPitch, pitch);
-        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        CU(dense_norms());
         return DPSVM_OK;
     }
     if (!c->d_sp_row_nnz) CU(cudaMalloc(&c->d_sp_row_nnz, sizeof(int) * (size_t)n));
@@ -300,7 +306,7 @@ int sparse_setup(dpsvm_ctx* c)
     // iteration; the sparse sweep sustains about three quarters of the dense sweep's byte rate, so the break-even
     // is near 0.75 and the threshold sits a little below it.
     if (mode == 0 && 6.0 * (double)total > kSparseAutoRatio * dense_bytes) {
-        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        CU(dense_norms());
         return DPSVM_OK;
     }
     const int lanes = lanes_for((double)total / (double)n);
@@ -322,7 +328,7 @@ int sparse_setup(dpsvm_ctx* c)
     const unsigned int total_steps = h_off[n_units];
     const double stream_bytes = 192.0 * (double)total_steps;
     if (mode == 0 && stream_bytes > kSparseAutoRatio * dense_bytes) {
-        CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
+        CU(dense_norms());
         return DPSVM_OK;
     }
     const size_t val_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(float));

@@ -175,6 +175,13 @@ typedef struct {
                                         The two layouts add the same non-zero products in a different, fixed order
                                         (see dpsvm_layout_info); results agree to fp32 rounding of the dot products. */
 
+#define DPSVM_FLAG_X_MIRROR 32       /* with DPSVM_FLAG_X_SHARD_ONLY on a multi-GPU run: the upload still brings only the owned
+                                        rows, but every rank then copies the OTHER ranks' rows (with their labels and |x|^2) device
+                                        to device over NVLink, so that each GPU holds all of X -- what the reference does through the
+                                        host (svmTrain.cu:344).  The sweep still reads only the owned shard; the two rows of the
+                                        selected pair then come from local memory and the per-iteration exchange shrinks to 48 bytes
+                                        per rank (see dpsvm_comm_transport).  Costs 4*N*pitch bytes per GPU; every rank or none. */
+
 int dpsvm_create(const dpsvm_params* params, dpsvm_ctx** out);
 int dpsvm_destroy(dpsvm_ctx* ctx);
 
@@ -327,9 +334,15 @@ int dpsvm_smo_iteration_noalloc(const dpsvm_iteration_args* args, void* stream);
 int dpsvm_comm_unique_id(unsigned char id[DPSVM_COMM_ID_BYTES]);
 int dpsvm_comm_init(dpsvm_ctx* ctx, const unsigned char id[DPSVM_COMM_ID_BYTES], int rank, int world);
 /* Which transport the per-iteration exchange uses: 0 = none (single GPU), 1 = NCCL all-gather
- * captured in the graph, 2 = peer memory (the pass's last CTA stores the candidate package into every
- * rank's CUDA-IPC-mapped mailbox over NVLink; the control kernel waits on arrival flags). Peer memory
- * is the default and is chosen only if every rank could map every peer; DPSVM_EXCHANGE=nccl forces 1. */
+ * captured in the graph, 2 = peer memory with the candidate rows in the package (the last CTA of the pass, or CTA 0
+ * of the resident loop, stores keys, scalars and both candidate rows into every rank's CUDA-IPC-mapped mailbox over
+ * NVLink and raises a flag), 3 = peer memory with X mirrored (DPSVM_FLAG_X_MIRROR): only the packed keys and the two
+ * alphas travel, as six 8-byte words per rank that each carry their own sequence number -- no fence, no flag, one
+ * one-way trip.  Peer memory is the default and is chosen only if every rank could map every peer; DPSVM_EXCHANGE=nccl
+ * on any rank forces 1 on all.
+ * Every device-side wait for another rank (or another CTA) is bounded by DPSVM_TIMEOUT_MS (default 10 000): ranks
+ * must enter dpsvm_train / dpsvm_train_async within that window of each other (put a host-side barrier before the
+ * call if their setup times differ); on expiry the loop stops and the call returns DPSVM_ERR_COMM. */
 int dpsvm_comm_transport(dpsvm_ctx* ctx);
 
 #ifdef __cplusplus

@@ -29,6 +29,9 @@ def _free_port():
 def _worker(rank, world, port, name, cache, exchange, out_dir, layout="auto"):
     graph_loop = exchange.endswith("+graph")
     exchange = exchange.split("+")[0]
+    mirror = exchange == "p2p-ll"          # X mirrored on every rank, candidates as flagged words
+    if mirror:
+        exchange = "p2p"
     os.environ["DPSVM_LAYOUT"] = layout
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -49,7 +52,7 @@ def _worker(rank, world, port, name, cache, exchange, out_dir, layout="auto"):
     dist.broadcast_object_list(ids, src=0)
     with capi.Trainer(n, d, float(g["c"]), float(g["gamma"]), float(g["epsilon"]), max_iter=int(g["max_iter"]), cache_size=cache,
                       shard_rows=cnt, shard_start=lo, device=rank,
-                      flags=capi.FLAG_X_SHARD_ONLY | (capi.FLAG_GRAPH_LOOP if graph_loop else 0)) as t:
+                      flags=capi.FLAG_X_SHARD_ONLY | (capi.FLAG_GRAPH_LOOP if graph_loop else 0) | (capi.FLAG_X_MIRROR if mirror else 0)) as t:
         t.comm_init(ids[0], rank, world)
         t.upload(np.ascontiguousarray(g["x"][lo:lo + cnt]), np.ascontiguousarray(g["y"][lo:lo + cnt]))
         st = t.train()
@@ -66,12 +69,16 @@ def _worker(rank, world, port, name, cache, exchange, out_dir, layout="auto"):
     ("mnist_512", 10, "p2p+graph", "auto"), ("adult_2048", 0, "p2p+graph", "auto"),
     ("mnist_512", 10, "nccl", "auto"), ("odd_d_333x37", 0, "nccl", "auto"),
     # the same exchanges with every rank sweeping the sparse stream of its shard (goldens are small: auto keeps them dense)
-    ("mnist_512", 10, "p2p", "sparse"), ("adult_2048", 0, "p2p+graph", "sparse"), ("mnist_512", 0, "nccl", "sparse")])
+    ("mnist_512", 10, "p2p", "sparse"), ("adult_2048", 0, "p2p+graph", "sparse"), ("mnist_512", 0, "nccl", "sparse"),
+    # X mirrored on every rank (DPSVM_FLAG_X_MIRROR): 48-byte flagged-word exchange, pair rows from local memory
+    ("mnist_512", 0, "p2p-ll", "auto"), ("adult_2048", 10, "p2p-ll", "auto"), ("odd_d_333x37", 4, "p2p-ll", "auto"),
+    ("dups_96x16", 2, "p2p-ll", "auto"), ("mnist_512", 10, "p2p-ll+graph", "auto"), ("adult_2048", 0, "p2p-ll+graph", "sparse"),
+    ("mnist_1024_tight", 64, "p2p-ll", "sparse")])
 def test_sharded_training_equals_single_gpu(golden, tmp_path, monkeypatch, name, cache, exchange, layout):
     import torch.multiprocessing as mp
     from dpsvm_b200 import capi
     monkeypatch.setenv("DPSVM_LAYOUT", layout)
-    world = min(_ngpu(), 4 if name == "adult_2048" else 2)
+    world = min(_ngpu(), 4 if name == "adult_2048" else (3 if name == "odd_d_333x37" else 2))
     mp.spawn(_worker, args=(world, _free_port(), name, cache, exchange, str(tmp_path), layout), nprocs=world, join=True)
     g = golden(name)
     with capi.Trainer(int(g["n"]), int(g["d"]), float(g["c"]), float(g["gamma"]), float(g["epsilon"]),
@@ -82,7 +89,7 @@ def test_sharded_training_equals_single_gpu(golden, tmp_path, monkeypatch, name,
     parts = [np.load(tmp_path / ("r%d.npz" % r)) for r in range(world)]
     for p in parts:
         assert str(p["transport"]) == exchange.split("+")[0]      # peer mapping must actually be in use when asked for
-        assert bool(p["resident"]) == (exchange == "p2p")         # resident loop over peer memory, graph loop otherwise
+        assert bool(p["resident"]) == (exchange in ("p2p", "p2p-ll"))   # resident loop over peer memory, graph loop otherwise
         assert int(p["it"]) == st.num_iter and int(p["conv"]) == st.converged and float(p["b"]) == st.b
         assert int(p["hits"]) == st.cache_hits
     assert np.array_equal(np.concatenate([p["alpha"] for p in parts]), alpha)
