@@ -47,7 +47,7 @@ static void free_all(dpsvm_ctx* c)
     if (c->graph) cudaGraphDestroy(c->graph);
     cudaFree(c->d_x); cudaFree(c->d_xsq); cudaFree(c->d_y); cudaFree(c->d_alpha); cudaFree(c->d_f);
     cudaFree(c->d_sel_rows); cudaFree(c->d_ext_rows); cudaFree(c->d_keys); cudaFree(c->d_keys_copy); cudaFree(c->d_st);
-    cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line);
+    cudaFree(c->cache.data); cudaFree(c->cache.line_of_key); cudaFree(c->cache.key_of_line); cudaFree(c->d_cache_stamp);
     cudaFree(c->cache.prev); cudaFree(c->cache.next); cudaFree(c->cache.meta);
     cudaFree(c->d_slots); cudaFree(c->d_barrier); cudaFree(c->d_lru); cudaFree(c->d_trace);
     sparse_release(c);
@@ -206,12 +206,15 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     a.lru_key = c->d_lru;
     a.lru_stamp = c->d_lru + kResCacheLines;
     a.lru_meta = c->d_lru + 2 * kResCacheLines;
+    a.cache_direct = (c->d_cache_stamp && c->cache.lines >= c->p.num_train_data) ? 1 : 0;
+    a.cache_stamp = c->d_cache_stamp;
     a.sp = c->sp;
     a.world = 1;
     a.timeout_ns = c->timeout_ns;
+    a.prefetch_mode = env_int("DPSVM_PREFETCH", 0);
     if (c->world > 1 && !comm_fill_resident(c, &a)) return fail(DPSVM_ERR_STATE, "resident loop needs the peer-memory exchange");
     const int trace_on = env_int("DPSVM_TRACE", 0);
-    if (trace_on && !c->d_trace) { CU(cudaMalloc(&c->d_trace, sizeof(unsigned long long) * 8 * 1024)); CU(cudaMemset(c->d_trace, 0, sizeof(unsigned long long) * 8 * 1024)); }
+    if (trace_on && !c->d_trace) { CU(cudaMalloc(&c->d_trace, sizeof(unsigned long long) * 16 * 1024)); CU(cudaMemset(c->d_trace, 0, sizeof(unsigned long long) * 16 * 1024)); }
     unsigned long long* d_trace = c->d_trace;
     a.trace = trace_on ? d_trace : nullptr;
     a.trace_iter = env_int("DPSVM_TRACE_ITER", 20);
@@ -228,37 +231,50 @@ static int launch_resident_chunk(dpsvm_ctx* c)
     }
     c->launched_iters += c->chunk;
     if (trace_on && c->launched_iters == (long long)c->chunk * trace_on) {
-        // debugging aid: phase times of one iteration, per CTA (chain | sweep | barrier wait), in us
-        std::vector<unsigned long long> h(8 * 1024);
+        // debugging aid: phase times of one iteration, per CTA, in us.  Stamps (smo_resident.cu): 0 iteration start,
+        // 1 pair rows landed, 2 |x_hi - x_lo|^2 partial sums done, 3 pass scalars ready, 4 sweep done, 5 grid barrier
+        // passed, 6 slots merged, 7 candidates pushed (multi-GPU), 8 peers' candidates merged (multi-GPU)
+        std::vector<unsigned long long> h(16 * 1024);
         CU(cudaStreamSynchronize(c->stream));
-        CU(cudaMemcpy(h.data(), d_trace, sizeof(unsigned long long) * 8 * 1024, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(h.data(), d_trace, sizeof(unsigned long long) * 16 * 1024, cudaMemcpyDeviceToHost));
         const int G = device_sm_count();
-        double mx[3] = {0, 0, 0}, mn[3] = {1e30, 1e30, 1e30}, sum[3] = {0, 0, 0};
+        static const char* names[8] = {"rows by TMA", "partial sums", "eta/alpha/LRU", "sweep", "barrier wait", "slot merge", "push", "remote wait+merge"};
+        const int phases = c->world > 1 ? 8 : 6;
+        double mx[8], mn[8], sum[8];
+        for (int k = 0; k < 8; ++k) { mx[k] = 0; mn[k] = 1e30; sum[k] = 0; }
         unsigned long long t_first = ~0ull, t_last = 0;
         for (int b = 0; b < G; ++b) {
-            for (int k = 0; k < 3; ++k) {
-                const double us = (double)(h[b * 8 + k + 1] - h[b * 8 + k]) * 1e-3;
+            for (int k = 0; k < phases; ++k) {
+                if (k == 6 && b != 0) continue;       // only CTA 0 pushes
+                const double us = (double)(long long)(h[b * 16 + k + 1] - h[b * 16 + k]) * 1e-3;
                 mx[k] = us > mx[k] ? us : mx[k]; mn[k] = us < mn[k] ? us : mn[k]; sum[k] += us;
             }
-            t_first = h[b * 8] < t_first ? h[b * 8] : t_first;
-            t_last = h[b * 8 + 3] > t_last ? h[b * 8 + 3] : t_last;
+            t_first = h[b * 16] < t_first ? h[b * 16] : t_first;
+            t_last = h[b * 16 + 6] > t_last ? h[b * 16 + 6] : t_last;
         }
         if (const char* dump = getenv("DPSVM_TRACE_DUMP")) {
             if (FILE* fp = fopen(dump, "a")) {
-                for (int b = 0; b < G; ++b)
-                    fprintf(fp, "%d %d %.3f %.3f %.3f\n", a.trace_iter, b, (double)(h[b * 8 + 1] - h[b * 8]) * 1e-3,
-                            (double)(h[b * 8 + 2] - h[b * 8 + 1]) * 1e-3, (double)(h[b * 8 + 3] - h[b * 8 + 2]) * 1e-3);
+                for (int b = 0; b < G; ++b) {
+                    fprintf(fp, "%d %d", a.trace_iter, b);
+                    for (int k = 0; k < phases; ++k) fprintf(fp, " %.3f", (double)(long long)(h[b * 16 + k + 1] - h[b * 16 + k]) * 1e-3);
+                    fprintf(fp, "\n");
+                }
                 fclose(fp);
             }
         }
-        fprintf(stderr, "[dpsvm trace] iteration %d over %d CTAs: chain min/avg/max %.2f/%.2f/%.2f us | sweep %.2f/%.2f/%.2f us | "
-                        "barrier wait %.2f/%.2f/%.2f us | first start -> last release %.2f us\n",
-                a.trace_iter, G, mn[0], sum[0] / G, mx[0], mn[1], sum[1] / G, mx[1], mn[2], sum[2] / G, mx[2],
-                (double)(t_last - t_first) * 1e-3);
-        if (c->world > 1)
-            fprintf(stderr, "[dpsvm trace] rank %d CTA0: local merge %.2f us after barrier | push %.2f us | remote wait+merge (CTA0 / CTA1) %.2f / %.2f us\n",
-                    c->rank, (double)(h[4] - h[3]) * 1e-3, (double)(h[5] - h[4]) * 1e-3, (double)(h[6] - h[5]) * 1e-3,
-                    (double)(h[8 + 6] - h[8 + 5]) * 1e-3);
+        fprintf(stderr, "[dpsvm trace] rank %d iteration %d over %d CTAs (min/avg/max us):", c->rank, a.trace_iter, G);
+        for (int k = 0; k < phases; ++k)
+            fprintf(stderr, " %s %.2f/%.2f/%.2f |", names[k], mn[k], k == 6 ? sum[k] : sum[k] / G, mx[k]);
+        {
+            double mn9 = 1e30, mx9 = 0, sum9 = 0, sp = 0, spmax = 0;
+            for (int b = 0; b < G; ++b) {
+                const double us = (double)(long long)(h[b * 16 + 9] - h[b * 16 + 4]) * 1e-3;
+                mn9 = us < mn9 ? us : mn9; mx9 = us > mx9 ? us : mx9; sum9 += us;
+                sp += (double)h[b * 16 + 10]; spmax = (double)h[b * 16 + 10] > spmax ? (double)h[b * 16 + 10] : spmax;
+            }
+            fprintf(stderr, " [slot stored + prefetch issued %.2f/%.2f/%.2f after sweep; thread 0 re-polled its slot %.1f times on average, %.0f at most] |", mn9, sum9 / G, mx9, sp / G, spmax);
+        }
+        fprintf(stderr, " first start -> last merge %.2f us\n", (double)(t_last - t_first) * 1e-3);
     }
     return DPSVM_OK;
 }
@@ -321,6 +337,7 @@ static int init_cache(dpsvm_ctx* c)
     CacheDev& k = c->cache;
     if (k.lines <= 0) return DPSVM_OK;
     CU(cudaMemsetAsync(k.line_of_key, 0xFF, sizeof(int) * (size_t)c->p.num_train_data, c->stream));
+    if (c->d_cache_stamp) CU(cudaMemsetAsync(c->d_cache_stamp, 0, sizeof(int) * (size_t)c->p.num_train_data, c->stream));
     CU(cudaMemsetAsync(k.meta, 0, sizeof(int) * kCacheMetaInts, c->stream));
     CU(cudaMemsetAsync(c->d_lru, 0, sizeof(int) * (2 * kResCacheLines + 2), c->stream));
     const int minus1[2] = {-1, -1};   // pageable source: staged before the call returns
@@ -335,6 +352,7 @@ static int reset_state(dpsvm_ctx* c)
     CU(cudaMemsetAsync(c->d_alpha, 0, sizeof(float) * (size_t)c->res_n, c->stream));
     CU(launch_init_state(c->d_y + off, c->p.shard_rows, nullptr, c->d_f, c->stream));
     CU(cudaMemsetAsync(c->d_st, 0, sizeof(DevState), c->stream));
+    CU(cudaMemsetAsync(c->d_slots, 0, 2 * 1024 * sizeof(ResSlot), c->stream));     // iteration numbers restart: no stale slot may look valid
     int rc = set_stop_at(c, INT_MAX);
     if (rc != DPSVM_OK) return rc;
     rc = init_cache(c);
@@ -452,13 +470,14 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     {
         const char* lp = getenv("DPSVM_LOOP");
         const bool want_graph = (p->flags & (DPSVM_FLAG_GRAPH_LOOP | DPSVM_FLAG_NO_GRAPH)) || (lp && strcmp(lp, "graph") == 0);
-        c->loop_resident = (!want_graph && resident_supported(c->pitch / 4, p->cache_size >= 2 ? p->cache_size : 0)) ? 1 : 0;
+        c->loop_resident = (!want_graph && resident_supported(c->pitch / 4, p->cache_size >= 2 ? p->cache_size : 0, p->num_train_data)) ? 1 : 0;
     }
     if (c->chunk > 1 && (c->chunk & 1)) c->chunk += 1;   // even chunks keep the direction alternating across launches
     c->world = 1; c->rank = 0;
     // the reference with one line aliases the hi and lo buffers (latent bug, cache.cu:82-105): a
     // single line cannot hold both rows of an iteration, so 1 behaves as "cache off" here.
     c->cache.lines = p->cache_size >= 2 ? p->cache_size : 0;
+    if (c->cache.lines > p->num_train_data) c->cache.lines = p->num_train_data;     // one line per row is all there is to cache
     c->cache.line_stride = ((size_t)p->shard_rows + 31) / 32 * 32;
 
 #define CUC(call)                                                                                        \
@@ -494,6 +513,7 @@ int dpsvm_create(const dpsvm_params* p, dpsvm_ctx** out)
     if (c->cache.lines > 0) {
         CUC(cudaMalloc(&c->cache.data, sizeof(float) * c->cache.line_stride * (size_t)c->cache.lines));
         CUC(cudaMalloc(&c->cache.line_of_key, sizeof(int) * (size_t)p->num_train_data));
+        if (c->cache.lines >= p->num_train_data) CUC(cudaMalloc(&c->d_cache_stamp, sizeof(int) * (size_t)p->num_train_data));
         CUC(cudaMalloc(&c->cache.key_of_line, sizeof(int) * (size_t)c->cache.lines));
         CUC(cudaMalloc(&c->cache.prev, sizeof(int) * (size_t)c->cache.lines));
         CUC(cudaMalloc(&c->cache.next, sizeof(int) * (size_t)c->cache.lines));

@@ -35,6 +35,7 @@ struct dpsvm_ctx {
     int* h_small = nullptr;                 // pinned scratch
 
     dpsvm::CacheDev cache{};
+    int* d_cache_stamp = nullptr;   // resident loop, cache with a line per row: [N] 0 = empty, else 1 + filling iteration
 
     // sparse stream of the owned rows (smo_sparse.cu); sp.val == null: the sweep reads the dense rows
     dpsvm::SparseDev sp{};
@@ -42,6 +43,8 @@ struct dpsvm_ctx {
     unsigned short* d_sp_col = nullptr;
     unsigned int* d_sp_unit_off = nullptr;
     int* d_sp_cta_first = nullptr;
+    unsigned short* d_sp_perm = nullptr;     // SparseDev::perm followed by SparseDev::cnt
+    size_t sp_perm_cap = 0;
     int* d_sp_row_nnz = nullptr;             // build scratch, kept for the next upload
     unsigned int* d_sp_unit_steps = nullptr;
     unsigned long long* d_sp_total = nullptr;

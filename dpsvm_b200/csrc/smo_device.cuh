@@ -76,6 +76,14 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned 
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void st_relaxed_gpu_v2u64(unsigned long long* p, unsigned long long v0, unsigned long long v1)
+{
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v0), "l"(v1) : "memory");
+}
+__device__ __forceinline__ void ld_relaxed_gpu_v2u64(const unsigned long long* p, unsigned long long& v0, unsigned long long& v1)
+{
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(v0), "=l"(v1) : "l"(p) : "memory");
+}
 __device__ __forceinline__ unsigned long long global_timer_ns()
 {
     unsigned long long t;
@@ -257,14 +265,17 @@ __device__ __forceinline__ void sp_next(SpCursor& q, const SEQ& seq)
     if (++q.c >= q.nc) { q.k += seq.k_stride; sp_open(q, seq); }
 }
 
-// Resident loop: local units of one CTA, first steps in shared memory, forward or reverse.
+// Resident loop: the units one warp slot sweeps in its CTA (SparseDev::perm), first steps in shared memory, forward
+// or reverse.  Sequence index k = 0 .. k_end - 1 runs over the slot's list.
 struct SpSeqCta {
-    int k_first, k_stride, k_end;       // k_end = units of this CTA
-    const unsigned int* uoff;           // [k_end + 1] in shared memory
+    int k_first, k_stride, k_end;       // 0, 1, units of this slot
+    const unsigned int* uoff;           // [units of the CTA + 1] in shared memory
+    const unsigned short* perm;         // this slot's first entry; consecutive entries are perm_step apart
+    int perm_step;
     bool rev;
     int hint;                           // 0: no eviction hints at all
     unsigned int pin_steps;             // steps of the CTA's range (from its start) kept in L2
-    __device__ __forceinline__ int local(int k) const { return rev ? (k_end - 1 - k) : k; }
+    __device__ __forceinline__ int local(int k) const { return (int)perm[(rev ? (k_end - 1 - k) : k) * perm_step]; }
     __device__ __forceinline__ void unit(int k, unsigned int& beg, int& steps) const
     {
         const int lu = local(k);

@@ -40,6 +40,12 @@ struct SparseDev {
     const unsigned short* col;
     const unsigned int* unit_off;   // [n_units + 1] first step of each unit
     const int* cta_first;       // [grid + 1] first unit of each CTA of the resident loop (balanced by steps)
+    // resident loop: which units of its CTA each warp sweeps.  Units differ in length (whole chunks of 8 steps), so the
+    // host deals them longest-first to the least loaded of the CTA's 16 warp slots; slot s sweeps
+    // perm[cta][j * 16 + s], j = 0 .. cnt[cta][s] - 1 (local unit numbers, ascending), slot 0 carrying the most.
+    const unsigned short* perm; // [grid][perm_stride]
+    const unsigned short* cnt;  // [grid][16]
+    int perm_stride;            // 16 * the largest cnt
     int lanes;                  // G: 4, 8, 16 or 32
     int n_units;
     int grid;                   // CTAs cta_first was computed for
@@ -182,12 +188,14 @@ struct CtlDev {
 constexpr int kResThreads = 512;
 constexpr int kResCacheLines = 64;      // largest kernel-row cache whose LRU table is replicated per CTA
 
-struct ResSlot {                        // what a CTA publishes after its sweep
-    unsigned long long key_up, key_low; // block-best packed keys
-    float a_up, a_low;                  // alpha of those two rows
-    int pad[2];
+// What a CTA publishes after its sweep: its block-best packed keys and the alpha of those two rows, as six flagged
+// 8-byte words (data in the low half, 1 + the global iteration number in the high half; see LLDev).  A word is valid
+// the moment a reader sees the right number in it, so the writer needs no fence and the readers no barrier: the
+// slot array IS the grid barrier.  w[0],w[1] = key_up (high, low word)  w[2],w[3] = key_low  w[4],w[5] = alpha_up, alpha_low.
+struct ResSlot {
+    unsigned long long w[8];
 };
-static_assert(sizeof(ResSlot) == 32, "ResSlot is 32 bytes");
+static_assert(sizeof(ResSlot) == 64, "ResSlot is 64 bytes");
 
 struct ResidentDev {
     const float4* x4;           // [n x pitch4] owned rows
@@ -211,11 +219,14 @@ struct ResidentDev {
     int* lru_key;               // [cache_lines]
     int* lru_stamp;             // [cache_lines]
     int* lru_meta;              // [2] size, clock
+    int cache_direct;           // 1: one line per global row (cache_lines >= N): line = key, nothing is ever evicted
+    int* cache_stamp;           // [N global] 0 = line not filled, else 1 + the iteration that filled it
     // filled by the launcher
     int res_units;              // units of X each CTA keeps in shared memory
     int pin_units;              // streamed units per CTA loaded L2::evict_last
     int stream_evict_first;
     int parity0;                // sweep direction of the launch's first iteration
+    int prefetch_mode;          // next sweep's first loads: 0 issued right after the slot store, 1 after the slots have been read, 2 not at all
     // multi-GPU (world > 1): the pair comes from the peer-memory mailbox (see PushDev); CTA 0 publishes
     int world, rank;
     const PushDev* push;
@@ -229,7 +240,7 @@ struct ResidentDev {
     SparseDev sp;               // sp.val != null: sweep the sparse stream instead of x4
 };
 
-bool resident_supported(int pitch4, int cache_lines);
+bool resident_supported(int pitch4, int cache_lines, int n_total);
 int resident_grid();            // CTAs of the resident loop on the current device (one per SM)
 cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream_t s);
 cudaError_t launch_resident(const ResidentDev& a, int variant, cudaStream_t s);

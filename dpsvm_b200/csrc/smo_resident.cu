@@ -141,8 +141,11 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     // sparse: the pair interleaved, (x_hi[c], x_lo[c]), then the first step of each of this CTA's units
     float2* s_hl = reinterpret_cast<float2*>(s_lo + CAP4);
     unsigned int* s_uoff = reinterpret_cast<unsigned int*>(s_hl + CAP4 * 4);
+    // ... the units each warp slot sweeps (SparseDev::perm, cnt) ...
+    unsigned short* s_perm = reinterpret_cast<unsigned short*>(s_uoff + ((a.sp.max_cta_units + 1 + 3) & ~3));
+    unsigned short* s_cnt = s_perm + ((a.sp.perm_stride + 7) & ~7);
     // ... then the first chunks of this CTA's part of the stream, kept on chip for the whole launch
-    float4* s_rval = reinterpret_cast<float4*>(s_uoff + ((a.sp.max_cta_units + 1 + 3) & ~3));
+    float4* s_rval = reinterpret_cast<float4*>(s_cnt + 16);
     uint4* s_rcol = reinterpret_cast<uint4*>(s_rval + (size_t)a.sp.res_chunks * 64);
     // their per-row scalars live on chip as well (a warp round on a stationary unit then touches no
     // global memory at all): |x|^2, y, f, alpha -- [a.res_units * RPW] each, after the rows
@@ -154,14 +157,19 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ float s_part[8];
     __shared__ Cand s_cand[2][NW];
+    __shared__ Cand s_cand2[2][NW];
     __shared__ int s_flag;
     __shared__ int s_lru_key[kResCacheLines], s_lru_stamp[kResCacheLines], s_lru_meta[2];
-    __shared__ PassScalars s_ps;
+    __shared__ float s_delta[4];                       // delta_hi, delta_lo, alpha_hi_new, alpha_lo_new of this iteration
+    __shared__ struct { int both_hit; float* line_hi; float* line_lo; float xsq_hi, xsq_lo; } s_early;   // known before eta
     __shared__ unsigned int s_ll[kMaxPeers * kLLWords];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sub = SPARSE ? lane % SGL : lane % LPR, grp = SPARSE ? lane / SGL : lane / LPR;
     const int G = gridDim.x, cta = blockIdx.x;
+    // units are dealt to the warps round-robin starting from the LAST warp: when the count is not a multiple of NW the
+    // spare time falls to warp 0, whose thread 0 computes eta while the others already sweep
+    const int wslot = NW - 1 - warp;
     DevState* st = a.st;
 
     // ---- launch-time state (identical in every CTA; nobody writes it before the first barrier) ----
@@ -263,6 +271,8 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     SpRes sp_res{0u, 0u, s_rval, s_rcol};
     if (SPARSE) {
         for (int i = tid; i <= u1 - u0; i += kResThreads) s_uoff[i] = a.sp.unit_off[u0 + i];
+        for (int i = tid; i < a.sp.perm_stride; i += kResThreads) s_perm[i] = a.sp.perm[(size_t)cta * a.sp.perm_stride + i];
+        if (tid < NW) s_cnt[tid] = a.sp.cnt[cta * NW + tid];
         const unsigned int c_first = a.sp.unit_off[u0] / kSpChunk, c_end = a.sp.unit_off[u1] / kSpChunk;
         sp_res.chunk0 = c_first;
         sp_res.n = min(c_end - c_first, a.sp.res_chunks);
@@ -294,7 +304,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             s_ralpha[i] = ok ? a.alpha[row] : 0.f;
         }
     }
-    if (a.cache_lines > 0) {
+    if (a.cache_lines > 0 && !a.cache_direct) {
         for (int i = tid; i < a.cache_lines; i += kResThreads) { s_lru_key[i] = a.lru_key[i]; s_lru_stamp[i] = a.lru_stamp[i]; }
         if (tid < 2) s_lru_meta[tid] = a.lru_meta[tid];
     }
@@ -360,7 +370,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         if (a.trace && it == a.trace_iter && tid == 0) {
             unsigned long long t;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            a.trace[(size_t)cta * 8 + which] = t;
+            a.trace[(size_t)cta * 16 + which] = t;
         }
     };
 
@@ -370,11 +380,21 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const int r_hi = i_hi - a.index_base, r_lo = i_lo - a.index_base;     // may lie outside [0, n) on a multi-GPU run
         int y_hi, y_lo;
         float xsq_hi, xsq_lo;
+        // kernel-row cache, decided while the rows are in flight (it needs the pair only): a table of up to 64 lines is a
+        // replicated state machine run by thread 0; a cache with a line for EVERY row never evicts, its line is the
+        // key itself, and "filled in an earlier iteration" is read from a stamp by every thread for itself
+        int hit_hi = 0, hit_lo = 0;
+        if (a.cache_direct) {
+            // stamp = 1 + the iteration that filled the line; this iteration's own stamp (written below by CTA 0, possibly
+            // before another CTA reads it) does not count as a hit
+            const int s_h = __ldcg(a.cache_stamp + i_hi), s_l = __ldcg(a.cache_stamp + i_lo);
+            hit_hi = (s_h != 0 && s_h <= num_iter);
+            hit_lo = (i_lo == i_hi) || (s_l != 0 && s_l <= num_iter);      // hi then lo (svmTrain.cu:203,238): the second lookup finds the first
+        }
         if (a.world > 1 && !ll_mode) {
             // rows travelled in the packages (written by peers over NVLink): plain L2 loads into smem
             for (int i = tid; i < a.pitch4; i += kResThreads) { s_hi[i] = __ldcg(m_src_hi + i); s_lo[i] = __ldcg(m_src_lo + i); }
             y_hi = m_y_hi; y_lo = m_y_lo; xsq_hi = m_xsq_hi; xsq_lo = m_xsq_lo;
-            __syncthreads();
         } else {
             if (tid == 0) {
                 const uint32_t bytes = (uint32_t)a.pitch4 * 16u;
@@ -384,8 +404,37 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             }
             y_hi = __ldg(a.y + r_hi); y_lo = __ldg(a.y + r_lo);
             xsq_hi = __ldg(a.xsq + r_hi); xsq_lo = __ldg(a.xsq + r_lo);
-            mbar_wait(&s_bar, (uint32_t)(it & 1));
         }
+        if (tid == 0) {
+            int both = 0;
+            float* l_hi_p = nullptr;
+            float* l_lo_p = nullptr;
+            if (a.cache_direct) {
+                float* p_hi = a.cache_data + (size_t)i_hi * a.line_stride;
+                float* p_lo = a.cache_data + (size_t)i_lo * a.line_stride;
+                if (hit_hi && hit_lo) { both = 1; l_hi_p = p_hi; l_lo_p = p_lo; }
+                else { if (!hit_hi) l_hi_p = p_hi; if (!hit_lo) l_lo_p = p_lo; }
+            } else if (a.cache_lines > 0) {
+                LruTable t{s_lru_key, s_lru_stamp, s_lru_meta};
+                const int l_hi = lru_lookup(t, a.cache_lines, i_hi, &hit_hi);      // hi then lo (svmTrain.cu:203,238)
+                const int l_lo = lru_lookup(t, a.cache_lines, i_lo, &hit_lo);
+                float* p_hi = a.cache_data + (size_t)l_hi * a.line_stride;
+                float* p_lo = a.cache_data + (size_t)l_lo * a.line_stride;
+                if (hit_hi && hit_lo) { both = 1; l_hi_p = p_hi; l_lo_p = p_lo; }
+                else { if (!hit_hi) l_hi_p = p_hi; if (!hit_lo && l_lo != l_hi) l_lo_p = p_lo; }
+            }
+            s_early.both_hit = both; s_early.line_hi = l_hi_p; s_early.line_lo = l_lo_p;
+            s_early.xsq_hi = xsq_hi; s_early.xsq_lo = xsq_lo;
+            if (a.cache_lines > 0) { cache_lookups += 2; cache_hits += hit_hi + hit_lo; }
+            if (a.cache_direct && cta == 0 && !(hit_hi && hit_lo)) {
+                if (!hit_hi) a.cache_stamp[i_hi] = num_iter + 1;
+                if (!hit_lo) a.cache_stamp[i_lo] = num_iter + 1;
+                __threadfence();        // ordered before this thread's slot store, which is what the other CTAs wait for
+            }
+        }
+        if (a.world > 1 && !ll_mode) __syncthreads();
+        else mbar_wait(&s_bar, (uint32_t)(it & 1));
+        stamp(it, 1);
         // |x_hi - x_lo|^2 exactly as the control kernel sums it: 256 strided partials, warp butterfly,
         // then the eight warp sums in order (svmTrain.cu:696-714 is the host original)
         if (tid < kCtlThreads) {
@@ -403,49 +452,50 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             if (lane == 0) s_part[warp] = part;
         }
         __syncthreads();
-        if (tid == 0) {
-            float norm_sq = 0.f;
+        stamp(it, 2);
+        const int both_hit = s_early.both_hit;
+        // From here every warp may sweep: the dot products need the pair only.  What the per-row epilogue needs on top --
+        // the two alpha deltas, i.e. eta -- is computed by thread 0 meanwhile and handed over through named barrier 1:
+        // warp 0 arrives once the values are in shared memory, every other warp joins right before its first epilogue.
+        bool have_deltas = false;
+        if (warp == 0) {
+            if (tid == 0) {
+                float norm_sq = 0.f;
 #pragma unroll
-            for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);
-            const float k_lh = (float)exp((double)__fmul_rn(-a.gamma, norm_sq));                 // svmTrain.cu:709
-            const float eta = __fsub_rn(__fadd_rn(1.0f, 1.0f), __fmul_rn(2.0f, k_lh));          // svmTrainMain.cpp:282
-            const float s = (float)(y_lo * y_hi);                                                // :289-295
-            const float a_lo_unc = __fadd_rn(a_lo_old, __fdiv_rn(__fmul_rn((float)y_lo, __fsub_rn(b_hi, b_lo)), eta));
-            const float a_hi_unc = __fadd_rn(a_hi_old, __fmul_rn(s, __fsub_rn(a_lo_old, a_lo_unc)));
-            const float a_lo_new = a_lo_unc < 0.0f ? 0.0f : (a_lo_unc > a.c ? a.c : a_lo_unc);
-            const float a_hi_new = a_hi_unc < 0.0f ? 0.0f : (a_hi_unc > a.c ? a.c : a_hi_unc);
-            // the CTA that owns a row stores its alpha (only that CTA ever reads it again)
-            const int row_lo0 = u0 * RPW, row_hi0 = min(u1 * RPW, a.n);
-            const int row_res = row_lo0 + res_units * RPW;       // rows below this are the on-chip slice
-            if (r_lo >= row_lo0 && r_lo < row_hi0) { a.alpha[r_lo] = a_lo_new; if (r_lo < row_res) s_ralpha[r_lo - row_lo0] = a_lo_new; }   // svmTrainMain.cpp:298-299
-            if (r_hi >= row_lo0 && r_hi < row_hi0) { a.alpha[r_hi] = a_hi_new; if (r_hi < row_res) s_ralpha[r_hi - row_lo0] = a_hi_new; }
-            PassScalars ps;
-            ps.active = 1; ps.both_hit = 0;
-            ps.delta_hi = __fmul_rn(__fsub_rn(a_hi_new, a_hi_old), (float)y_hi);
-            ps.delta_lo = __fmul_rn(__fsub_rn(a_lo_new, a_lo_old), (float)y_lo);
-            ps.xsq_hi = xsq_hi; ps.xsq_lo = xsq_lo;
-            ps.line_hi = nullptr; ps.line_lo = nullptr;
-            if (a.cache_lines > 0) {
-                LruTable t{s_lru_key, s_lru_stamp, s_lru_meta};
-                int hit_hi, hit_lo;
-                const int l_hi = lru_lookup(t, a.cache_lines, i_hi, &hit_hi);      // hi then lo (svmTrain.cu:203,238)
-                const int l_lo = lru_lookup(t, a.cache_lines, i_lo, &hit_lo);
-                cache_lookups += 2; cache_hits += hit_hi + hit_lo;
-                float* p_hi = a.cache_data + (size_t)l_hi * a.line_stride;
-                float* p_lo = a.cache_data + (size_t)l_lo * a.line_stride;
-                if (hit_hi && hit_lo) { ps.both_hit = 1; ps.line_hi = p_hi; ps.line_lo = p_lo; }
-                else { if (!hit_hi) ps.line_hi = p_hi; if (!hit_lo && l_lo != l_hi) ps.line_lo = p_lo; }
+                for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);
+                const float k_lh = (float)exp((double)__fmul_rn(-a.gamma, norm_sq));                 // svmTrain.cu:709
+                const float eta = __fsub_rn(__fadd_rn(1.0f, 1.0f), __fmul_rn(2.0f, k_lh));          // svmTrainMain.cpp:282
+                const float s = (float)(y_lo * y_hi);                                                // :289-295
+                const float a_lo_unc = __fadd_rn(a_lo_old, __fdiv_rn(__fmul_rn((float)y_lo, __fsub_rn(b_hi, b_lo)), eta));
+                const float a_hi_unc = __fadd_rn(a_hi_old, __fmul_rn(s, __fsub_rn(a_lo_old, a_lo_unc)));
+                const float lo_new = a_lo_unc < 0.0f ? 0.0f : (a_lo_unc > a.c ? a.c : a_lo_unc);
+                const float hi_new = a_hi_unc < 0.0f ? 0.0f : (a_hi_unc > a.c ? a.c : a_hi_unc);
+                // the CTA that owns a row stores its alpha (only that CTA ever reads it again)
+                const int row_lo0 = u0 * RPW, row_hi0 = min(u1 * RPW, a.n);
+                const int row_res = row_lo0 + res_units * RPW;       // rows below this are the on-chip slice
+                if (r_lo >= row_lo0 && r_lo < row_hi0) { a.alpha[r_lo] = lo_new; if (r_lo < row_res) s_ralpha[r_lo - row_lo0] = lo_new; }   // svmTrainMain.cpp:298-299
+                if (r_hi >= row_lo0 && r_hi < row_hi0) { a.alpha[r_hi] = hi_new; if (r_hi < row_res) s_ralpha[r_hi - row_lo0] = hi_new; }
+                s_delta[0] = __fmul_rn(__fsub_rn(hi_new, a_hi_old), (float)y_hi);
+                s_delta[1] = __fmul_rn(__fsub_rn(lo_new, a_lo_old), (float)y_lo);
+                s_delta[2] = hi_new; s_delta[3] = lo_new;
+                if (cta == 0) {
+                    st->i_hi = i_hi; st->i_lo = i_lo; st->eta = eta; st->b_hi = b_hi; st->b_lo = b_lo;
+                    st->num_iter = num_iter + 1;
+                    st->cache_hits = cache_hits; st->cache_lookups = cache_lookups;
+                }
+                __threadfence_block();
             }
-            s_ps = ps;
-            if (cta == 0) {
-                st->i_hi = i_hi; st->i_lo = i_lo; st->eta = eta; st->b_hi = b_hi; st->b_lo = b_lo;
-                st->num_iter = num_iter + 1;
-                st->cache_hits = cache_hits; st->cache_lookups = cache_lookups;
-            }
+            __syncwarp();
+            asm volatile("bar.arrive 1, %0;" ::"n"(kResThreads) : "memory");
+            have_deltas = true;
         }
-        __syncthreads();
-        const PassScalars sc = s_ps;
-        stamp(it, 1);
+        auto need_deltas = [&]() {          // warp-uniform; every warp runs it exactly once per iteration
+            if (!have_deltas) {
+                asm volatile("bar.sync 1, %0;" ::"n"(kResThreads) : "memory");
+                have_deltas = true;
+            }
+        };
+        stamp(it, 3);
 
         // ================= sweep over this CTA's rows =================
         Cand best_up{DPSVM_KEY_EMPTY, 0.f}, best_low{DPSVM_KEY_EMPTY, 0.f};
@@ -454,14 +504,19 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const int row_res_end = (u0 + res_units) * RPW;      // rows below this (and >= u0*RPW) are on chip
         auto epilogue = [&](int row, float dh, float dl, float xs, float fj, float al, int yj, bool store) {
             if (store) {
-                if (sc.line_hi) sc.line_hi[row] = dh;
-                if (sc.line_lo) sc.line_lo[row] = dl;
+                float* const l_hi_p = s_early.line_hi;
+                float* const l_lo_p = s_early.line_lo;
+                if (l_hi_p) l_hi_p[row] = dh;
+                if (l_lo_p) l_lo_p[row] = dl;
             }
-            const float arg_hi = __fsub_rn(__fadd_rn(xs, sc.xsq_hi), __fmul_rn(2.0f, dh));       // svmTrain.cu:128,130
-            const float arg_lo = __fsub_rn(__fadd_rn(xs, sc.xsq_lo), __fmul_rn(2.0f, dl));
+            // the row's alpha may have been read before thread 0 installed this iteration's two new values
+            if (row == r_lo) al = s_delta[3];                                                    // svmTrainMain.cpp:298-299,
+            if (row == r_hi) al = s_delta[2];                                                    // in that order
+            const float arg_hi = __fsub_rn(__fadd_rn(xs, s_early.xsq_hi), __fmul_rn(2.0f, dh));  // svmTrain.cu:128,130
+            const float arg_lo = __fsub_rn(__fadd_rn(xs, s_early.xsq_lo), __fmul_rn(2.0f, dl));
             const float rbf_hi = expf(__fmul_rn(-a.gamma, arg_hi));
             const float rbf_lo = expf(__fmul_rn(-a.gamma, arg_lo));
-            const float delta = __fadd_rn(__fmul_rn(sc.delta_hi, rbf_hi), __fmul_rn(sc.delta_lo, rbf_lo));   // :133-135
+            const float delta = __fadd_rn(__fmul_rn(s_delta[0], rbf_hi), __fmul_rn(s_delta[1], rbf_lo));   // :133-135
             const float f_new = __fadd_rn(fj, delta);
             a.f[row] = f_new;
             if (row < row_res_end) s_rf[row - u0 * RPW] = f_new;
@@ -476,19 +531,25 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const bool keep_going = b_lo > __fadd_rn(b_hi, __fmul_rn(2.0f, a.epsilon));
         const bool last_iter = !keep_going || (num_iter + 1) >= a.max_iter || (num_iter + 1) >= stop_at || (it + 1) >= a.chunk;
 
-        if (sc.both_hit) {
+        SpSeqCta seq_sp;                    // this warp's units in the sparse stream (unused by the dense sweep)
+        if constexpr (SPARSE) {
+            seq_sp.k_first = 0; seq_sp.k_stride = 1; seq_sp.k_end = (int)s_cnt[wslot];
+            seq_sp.uoff = s_uoff;
+            seq_sp.perm = s_perm + wslot; seq_sp.perm_step = NW;
+            seq_sp.rev = rev;
+            seq_sp.hint = a.stream_evict_first;
+            seq_sp.pin_steps = a.sp.pin_steps;
+        }
+        if (both_hit) {
             // both kernel rows cached: no X, 28 B per row
+            need_deltas();
             pre = false;
             const int row_b = u0 * RPW, row_e = min(u1 * RPW, a.n);
             for (int row = row_b + tid; row < row_e; row += kResThreads)
-                epilogue(row, sc.line_hi[row], sc.line_lo[row], __ldg(a.xsq + row), a.f[row], a.alpha[row], __ldg(a.y + row), false);
+                epilogue(row, s_early.line_hi[row], s_early.line_lo[row], __ldg(a.xsq + row), a.f[row], a.alpha[row], __ldg(a.y + row), false);
         } else if constexpr (SPARSE) {
-            SpSeqCta seq;
-            seq.k_first = warp; seq.k_stride = NW; seq.k_end = my_units;
-            seq.uoff = s_uoff;
+            SpSeqCta& seq = seq_sp;
             seq.rev = rev;
-            seq.hint = a.stream_evict_first;
-            seq.pin_steps = a.sp.pin_steps;
             if (!pre) sp_prefetch(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
             pre = false;
             sp_sweep<SGL>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
@@ -501,17 +562,11 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                     }
                 },
                 [&](int, float dh, float dl) {
+                    need_deltas();
                     if (eown) epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, true);
                 });
-            // the stream does not depend on the pair: this warp's first chunks of the NEXT iteration (which sweeps
-            // the other way) go in flight now and land during the barrier and the merge
-            if (!last_iter) {
-                seq.rev = !rev;
-                sp_prefetch(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
-                pre = true;
-            }
         } else {
-            for (int k = warp; k < my_units; k += NW) {
+            for (int k = wslot; k < my_units; k += NW) {
                 if (!pre) load_const(k, rev);
                 pre = false;
                 if (eown) {                      // state written by the previous iteration / this prologue
@@ -542,6 +597,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                         acc_lo[r] = __fadd_rn(acc_lo[r], __shfl_xor_sync(0xffffffffu, acc_lo[r], off));
                     }
                 }
+                need_deltas();
                 if (eown) {
                     float dh = acc_hi[0], dl = acc_lo[0];
 #pragma unroll
@@ -550,60 +606,89 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 }
             }
         }
-        // X does not depend on the pair: put the next iteration's first unit in flight now, so HBM keeps
-        // streaming while the barrier, the slot merge and the eta reduction run
-        if constexpr (!SPARSE) {
-            if (!last_iter && warp < my_units) { load_const(warp, !rev); pre = true; }
-        }
-
-        // ================= block best -> slot, grid barrier, merge =================
-        __syncthreads();
-        stamp(it, 2);
+        need_deltas();          // a warp without rows this iteration still takes part in the hand-over
+        // ================= block best -> slot; all slots -> next pair =================
         cand_warp_min(best_up);
         cand_warp_min(best_low);
         if (lane == 0) { s_cand[0][warp] = best_up; s_cand[1][warp] = best_low; }
+        if (tid == 0) s_flag = 1;
         __syncthreads();
-        const int slot_set = (it + 1) & 1;
+        stamp(it, 4);
+        num_iter += 1;
+        const unsigned int seq = (unsigned int)num_iter;            // >= 1: a cleared slot never looks valid
+        const unsigned long long tag = (unsigned long long)seq << 32;
+        ResSlot* const slot_set = a.slots + (size_t)(seq & 1u) * G;
         if (warp == 0) {
             Cand u = lane < NW ? s_cand[0][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
             Cand l = lane < NW ? s_cand[1][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
             cand_warp_min(u);
             cand_warp_min(l);
-            if (lane == 0) {
-                ResSlot s;
-                s.key_up = u.key; s.key_low = l.key; s.a_up = u.alpha; s.a_low = l.alpha; s.pad[0] = 0; s.pad[1] = 0;
-                a.slots[(size_t)slot_set * G + cta] = s;
+            // three 16-byte stores of two flagged words each; nothing to order, nothing to count
+            if (lane < 3) {
+                unsigned int d0, d1;
+                if (lane == 0) { d0 = (unsigned int)(u.key >> 32); d1 = (unsigned int)u.key; }
+                else if (lane == 1) { d0 = (unsigned int)(l.key >> 32); d1 = (unsigned int)l.key; }
+                else { d0 = __float_as_uint(u.alpha); d1 = __float_as_uint(l.alpha); }
+                st_relaxed_gpu_v2u64(&slot_set[cta].w[2 * lane], tag | d0, tag | d1);
             }
         }
-        num_iter += 1;
+        // The next sweep's first loads do not depend on the pair: they go in flight now -- behind this CTA's slot, so
+        // that the one message every other SM is waiting for is not queued after them -- and land during the merge.
+        auto prefetch_next = [&]() {
+            if constexpr (SPARSE) {
+                if (!last_iter) {
+                    seq_sp.rev = !rev;
+                    sp_prefetch(sp_ring, a.sp, sp_res, seq_sp, lane, pol_keep, pol_stream);
+                    pre = true;
+                }
+            } else {
+                if (!last_iter && wslot < my_units) { load_const(wslot, !rev); pre = true; }
+            }
+        };
+        if (a.prefetch_mode == 0) prefetch_next();
+        stamp(it, 9);
 
-        if (!grid_barrier(a.barrier, bar_target, &s_flag, a.timeout_ns)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
-        bar_target += (unsigned int)G;
-        stamp(it, 3);
-
-        // every CTA merges all slots: minimum packed key = lowest global index among equal f
+        // every CTA reads every slot until all of them carry this iteration's number, and merges them: minimum packed key =
+        // lowest global index among equal f
         Cand nxt_up, nxt_low;
         {
             Cand u{DPSVM_KEY_EMPTY, 0.f}, l{DPSVM_KEY_EMPTY, 0.f};
             for (int c = tid; c < G; c += kResThreads) {
-                const ResSlot* sp = a.slots + (size_t)slot_set * G + c;
-                const unsigned long long ku = __ldcg(&sp->key_up), kl = __ldcg(&sp->key_low);
-                cand_min(u, ku, __ldcg(&sp->a_up));
-                cand_min(l, kl, __ldcg(&sp->a_low));
+                const unsigned long long* w = slot_set[c].w;
+                unsigned long long v0, v1, v2, v3, v4, v5;
+                unsigned long long t0 = 0;
+                unsigned int spins = 0;
+                for (;;) {
+                    ld_relaxed_gpu_v2u64(w, v0, v1);
+                    ld_relaxed_gpu_v2u64(w + 2, v2, v3);
+                    ld_relaxed_gpu_v2u64(w + 4, v4, v5);
+                    const unsigned long long bad = ((v0 ^ tag) | (v1 ^ tag) | (v2 ^ tag) | (v3 ^ tag) | (v4 ^ tag) | (v5 ^ tag)) >> 32;
+                    if (bad == 0) break;
+                    if ((++spins & 0xFFu) == 0) {
+                        if (t0 == 0) t0 = global_timer_ns();
+                        else if (global_timer_ns() - t0 > a.timeout_ns) { s_flag = 0; break; }
+                    }
+                }
+                if (a.trace && it == a.trace_iter && tid == 0) a.trace[(size_t)cta * 16 + 10] = spins;
+                cand_min(u, (v0 << 32) | (unsigned int)v1, __uint_as_float((unsigned int)v4));
+                cand_min(l, (v2 << 32) | (unsigned int)v3, __uint_as_float((unsigned int)v5));
             }
+            if (tid == 0) stamp(it, 5);
+            if (a.prefetch_mode == 1) prefetch_next();
             cand_warp_min(u);
             cand_warp_min(l);
-            if (lane == 0) { s_cand[0][warp] = u; s_cand[1][warp] = l; }
+            if (lane == 0) { s_cand2[0][warp] = u; s_cand2[1][warp] = l; }
             __syncthreads();
+            if (!s_flag) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
             // every warp finishes the reduction for itself: no second barrier, no broadcast through shared memory
-            nxt_up = lane < NW ? s_cand[0][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
-            nxt_low = lane < NW ? s_cand[1][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
+            nxt_up = lane < NW ? s_cand2[0][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
+            nxt_low = lane < NW ? s_cand2[1][lane] : Cand{DPSVM_KEY_EMPTY, 0.f};
             cand_warp_min(nxt_up);
             cand_warp_min(nxt_low);
         }
         // multi-GPU: CTA 0 publishes this rank's candidates to every rank (also on the last iteration of the
         // launch: the next launch starts by waiting for exactly these packages)
-        stamp(it, 4);
+        stamp(it, 6);
         if (a.world > 1 && cta == 0) {
             if (ll_mode) {
                 // one 8-byte flagged word per thread and peer, straight from registers: nothing to fence, nothing to read
@@ -618,7 +703,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 push_package(*a.push, nxt_up.key, nxt_low.key, nxt_up.alpha, nxt_low.alpha, true, (unsigned int)num_iter);
             }
         }
-        stamp(it, 5);
+        stamp(it, 7);
         if (last_iter) {
             if (cta == 0 && tid == 0) {
                 a.keys[0] = nxt_up.key;
@@ -631,7 +716,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         }
         if (a.world > 1) {
             if (!acquire((unsigned int)num_iter)) { if (cta == 0 && tid == 0) { st->error = 1; st->done = 1; } return; }
-            stamp(it, 6);
+            stamp(it, 8);
         } else {
             unpack_key_up(nxt_up.key, &b_hi, &i_hi);
             unpack_key_low(nxt_low.key, &b_lo, &i_lo);
@@ -644,7 +729,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         }
         // (s_cand is next written after a whole sweep, with several block barriers in between)
     }
-    if (cta == 0 && a.cache_lines > 0) {
+    if (cta == 0 && a.cache_lines > 0 && !a.cache_direct) {
         __syncthreads();
         for (int i = tid; i < a.cache_lines; i += kResThreads) { a.lru_key[i] = s_lru_key[i]; a.lru_stamp[i] = s_lru_stamp[i]; }
         if (tid < 2) a.lru_meta[tid] = s_lru_meta[tid];
@@ -774,7 +859,9 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
     }
     const int s_smem_max = cfg.smem_max, s_grid = cfg.grid;
     if (a.sp.grid != s_grid) return cudaErrorInvalidValue;      // cta_first was balanced for another grid
-    const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int);
+    static_assert(kResThreads / 32 == 16, "SparseDev::perm deals the units of a CTA to 16 warp slots");
+    const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int) +
+                         (((size_t)a.sp.perm_stride + 7) & ~(size_t)7) * sizeof(unsigned short) + 16 * sizeof(unsigned short);
     if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;
     // the rest of shared memory holds the head of each CTA's part of the stream (1.5 KB per chunk)
     size_t res_bytes = (size_t)s_smem_max - fixed;
@@ -808,15 +895,17 @@ cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream
 
 int resident_grid() { return device_sm_count(); }
 
-bool resident_supported(int pitch4, int cache_lines)
+// Kernel-row caches the resident loop can run: none, a small one (replicated LRU table), or one with a line for
+// every row of the set (nothing is ever evicted: direct index).  In between, eviction needs one writer: graph loop.
+bool resident_supported(int pitch4, int cache_lines, int n_total)
 {
-    return pitch4 <= 256 && cache_lines <= kResCacheLines;
+    return pitch4 <= 256 && (cache_lines <= kResCacheLines || cache_lines >= n_total);
 }
 
 cudaError_t launch_resident(const ResidentDev& a, int variant, cudaStream_t s)
 {
     if (a.n <= 0) return cudaSuccess;
-    if (!resident_supported(a.pitch4, a.cache_lines)) return cudaErrorInvalidValue;
+    if (a.pitch4 > 256 || (a.cache_lines > kResCacheLines && !a.cache_direct)) return cudaErrorInvalidValue;
     if (a.sp.val) return launch_resident_sparse(a, variant, s);
     const DotGeom g = dot_geometry(a.pitch4);
     switch (g.lpr) {

@@ -219,7 +219,8 @@ cudaError_t launch_sparse_row_norms(const float* val, const unsigned int* unit_o
 void sparse_release(dpsvm_ctx* c)
 {
     cudaFree(c->d_sp_val); cudaFree(c->d_sp_col); cudaFree(c->d_sp_unit_off); cudaFree(c->d_sp_cta_first);
-    cudaFree(c->d_sp_row_nnz); cudaFree(c->d_sp_unit_steps); cudaFree(c->d_sp_total);
+    cudaFree(c->d_sp_row_nnz); cudaFree(c->d_sp_unit_steps); cudaFree(c->d_sp_total); cudaFree(c->d_sp_perm);
+    c->d_sp_perm = nullptr; c->sp_perm_cap = 0;
     c->d_sp_val = nullptr; c->d_sp_col = nullptr; c->d_sp_unit_off = nullptr; c->d_sp_cta_first = nullptr;
     c->d_sp_row_nnz = nullptr; c->d_sp_unit_steps = nullptr; c->d_sp_total = nullptr;
     c->sp_val_cap = c->sp_col_cap = c->sp_units_cap = 0;
@@ -357,6 +358,57 @@ int sparse_setup(dpsvm_ctx* c)
     if (!c->d_sp_cta_first) CU(cudaMalloc(&c->d_sp_cta_first, sizeof(int) * 1025));
     if (grid > 1024) return fail(DPSVM_ERR_LIMIT, "resident grid of %d CTAs", grid);
     CU(cudaMemcpyAsync(c->d_sp_cta_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice, s));
+    // ... and inside a CTA the units are dealt to its 16 warp slots longest first, each to the least loaded slot (units
+    // come in whole chunks of 8 steps, typically 5 or 6 of them: seven short units weigh what six long ones do, where a
+    // plain round-robin leaves some warps a whole unit behind).  A unit's weight is its steps plus a fixed part for the
+    // lane sums and the per-row epilogue.
+    constexpr int kSlots = 16;
+    constexpr unsigned int kUnitFixedSteps = 8;
+    if (max_units > 0xFFFF) return fail(DPSVM_ERR_LIMIT, "%d units in one CTA", max_units);
+    std::vector<std::vector<unsigned short>> slot_units((size_t)grid * kSlots);
+    int max_cnt = 0;
+    {
+        std::vector<int> order;
+        std::vector<std::pair<unsigned long long, int>> load(kSlots);
+        for (int b = 0; b < grid; ++b) {
+            const int ub = first[b], m = first[b + 1] - first[b];
+            order.resize((size_t)m);
+            for (int i = 0; i < m; ++i) order[(size_t)i] = i;
+            std::stable_sort(order.begin(), order.end(), [&](int p, int q) {
+                return (h_off[(size_t)ub + p + 1] - h_off[(size_t)ub + p]) > (h_off[(size_t)ub + q + 1] - h_off[(size_t)ub + q]); });
+            unsigned long long w[kSlots] = {};
+            std::vector<unsigned short> tmp[kSlots];
+            for (int i : order) {
+                int best = 0;
+                for (int t = 1; t < kSlots; ++t) if (w[t] < w[best]) best = t;
+                tmp[best].push_back((unsigned short)i);
+                w[best] += (unsigned long long)(h_off[(size_t)ub + i + 1] - h_off[(size_t)ub + i]) + kUnitFixedSteps;
+            }
+            for (int t = 0; t < kSlots; ++t) load[(size_t)t] = {w[t], t};
+            std::stable_sort(load.begin(), load.end(), [](const std::pair<unsigned long long, int>& p, const std::pair<unsigned long long, int>& q) { return p.first > q.first; });
+            for (int t = 0; t < kSlots; ++t) {
+                std::vector<unsigned short>& v = tmp[load[(size_t)t].second];
+                std::sort(v.begin(), v.end());            // stream order inside a slot (the sweep alternates its direction)
+                max_cnt = std::max(max_cnt, (int)v.size());
+                slot_units[(size_t)b * kSlots + t] = std::move(v);
+            }
+        }
+    }
+    const int perm_stride = kSlots * std::max(1, max_cnt);
+    std::vector<unsigned short> h_perm((size_t)grid * perm_stride, 0), h_cnt((size_t)grid * kSlots, 0);
+    for (int b = 0; b < grid; ++b)
+        for (int t = 0; t < kSlots; ++t) {
+            const std::vector<unsigned short>& v = slot_units[(size_t)b * kSlots + t];
+            h_cnt[(size_t)b * kSlots + t] = (unsigned short)v.size();
+            for (size_t j = 0; j < v.size(); ++j) h_perm[(size_t)b * perm_stride + j * kSlots + t] = v[j];
+        }
+    {
+        size_t cap = c->sp_perm_cap;
+        CU(grow(c->d_sp_perm, cap, sizeof(unsigned short) * (h_perm.size() + h_cnt.size())));
+        c->sp_perm_cap = cap;
+    }
+    CU(cudaMemcpyAsync(c->d_sp_perm, h_perm.data(), sizeof(unsigned short) * h_perm.size(), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(c->d_sp_perm + h_perm.size(), h_cnt.data(), sizeof(unsigned short) * h_cnt.size(), cudaMemcpyHostToDevice, s));
     // the owned rows are all the rows this rank holds here (a forced sparse layout with foreign rows resident keeps
     // the dense-order norms for those: they only ever serve as the partner's |x|^2 in another row's kernel value)
     if (foreign_rows) CU(launch_row_norms(c->d_x, c->res_n, pitch, c->d_xsq, s));
@@ -366,6 +418,7 @@ int sparse_setup(dpsvm_ctx* c)
     sp.val = c->d_sp_val; sp.col = c->d_sp_col; sp.unit_off = c->d_sp_unit_off; sp.cta_first = c->d_sp_cta_first;
     sp.lanes = lanes; sp.n_units = n_units; sp.grid = grid; sp.max_cta_units = max_units;
     sp.total_steps = total_steps; sp.pin_steps = 0; sp.res_chunks = 0;
+    sp.perm = c->d_sp_perm; sp.cnt = c->d_sp_perm + h_perm.size(); sp.perm_stride = perm_stride;
     c->sp = sp;
     return DPSVM_OK;
 }

@@ -523,12 +523,15 @@ def test_full_shape_properties(torch, oracle):
 # the two loops: resident (persistent cooperative kernel, default) vs CUDA graph of [control, pass]
 # ------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name,cache", [("mnist_512", 0), ("mnist_512", 10), ("adult_2048", 4), ("odd_d_333x37", 0),
-                                        ("dups_96x16", 2), ("tiny_3x5", 0), ("mnist_1024_tight", 64)])
+                                        ("dups_96x16", 2), ("tiny_3x5", 0), ("mnist_1024_tight", 64),
+                                        # a line for every row: the resident loop indexes the cache by the key itself
+                                        ("mnist_512", 512), ("adult_2048", 5000), ("dups_96x16", 96)])
 def test_resident_and_graph_loops_are_bit_identical(golden, name, cache, layout):
     g = golden(name)
     out = []
     for flags in (0, capi.FLAG_GRAPH_LOOP):
         with _trainer(g, cache_size=cache, flags=flags) as t:
+            assert t.loop_info()[0] is (flags == 0)        # these cache sizes all run in the resident loop
             st = t.train()
             a, f, _ = t.download()
             rv, keys = t.step1()
