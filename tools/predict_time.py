@@ -9,7 +9,7 @@ from dpsvm_b200 import capi, datagen
 for wl in ("adult32k", "mnist60k"):
     x, y, prm = datagen.make(wl)
     n, d = x.shape
-    with capi.Trainer(n, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=2000000, cache_size=0) as t:
+    with capi.Trainer(n, d, prm["c"], prm["gamma"], prm["epsilon"], max_iter=2000000, cache_size=n) as t:
         t.upload(x, y)
         st = t.train()
         alpha, _, _ = t.download(f=False)
