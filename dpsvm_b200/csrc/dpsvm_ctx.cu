@@ -543,7 +543,7 @@ static int finish_upload(dpsvm_ctx* c)
     if (rc != DPSVM_OK) return rc;
     if (!getenv("DPSVM_VARIANT")) {
         // L2 policy follows what the sweep actually reads: hints and a pinned prefix once that outgrows L2
-        const double mb = c->sp.val ? 192e-6 * (double)c->sp.total_steps : 4e-6 * (double)c->p.shard_rows * (double)c->pitch;
+        const double mb = c->sp.val ? 1e-6 * (double)c->sp.step_bytes * (double)c->sp.total_steps : 4e-6 * (double)c->p.shard_rows * (double)c->pitch;
         // a stream about the size of L2 is kept there whole (measured at 123 MB: 25.9 us per iteration with 120 MB
         // pinned, 27.2 with 96, 28.3 with 64); a larger one keeps a 32 MB prefix (profiles/r01_l2_sweep.md)
         const int pin_mb = (c->sp.val && mb <= 130.0) ? 120 : 32;
@@ -710,7 +710,7 @@ int dpsvm_layout_info(dpsvm_ctx* c, int* lanes, long long* nnz, long long* sweep
     if (!c->uploaded) return fail(DPSVM_ERR_STATE, "dpsvm_layout_info before dpsvm_upload");
     if (lanes) *lanes = c->sp.val ? c->sp.lanes : 0;
     if (nnz) *nnz = c->sp_nnz;
-    if (sweep_bytes) *sweep_bytes = c->sp.val ? 192ll * (long long)c->sp.total_steps : 4ll * c->p.shard_rows * (long long)c->pitch;
+    if (sweep_bytes) *sweep_bytes = c->sp.val ? (long long)c->sp.step_bytes * (long long)c->sp.total_steps : 4ll * c->p.shard_rows * (long long)c->pitch;
     return DPSVM_OK;
 }
 

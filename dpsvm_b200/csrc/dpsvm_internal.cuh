@@ -41,6 +41,8 @@ struct dpsvm_ctx {
     dpsvm::SparseDev sp{};
     float* d_sp_val = nullptr;
     unsigned short* d_sp_col = nullptr;
+    unsigned char* d_sp_col8 = nullptr;      // 8-bit column distances (+ a flag word at the end)
+    size_t sp_col8_cap = 0;
     unsigned int* d_sp_unit_off = nullptr;
     int* d_sp_cta_first = nullptr;
     unsigned short* d_sp_perm = nullptr;     // SparseDev::perm followed by SparseDev::cnt

@@ -182,9 +182,10 @@ static_assert(kSpChunk == 8, "a chunk is one 256-bit value load and one 128-bit 
 struct SpRes {
     unsigned int chunk0, n;
     const float4* val;
-    const uint4* col;
+    const void* col;         // uint4 [chunk][lane] (16-bit offsets) or uint2 [chunk][lane] (8-bit column deltas)
 };
 
+template <bool C8>
 __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpRes& res, unsigned int chunk, int lane, int keep, uint64_t pol)
 {
     const unsigned int rc = chunk - res.chunk0;
@@ -192,11 +193,11 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
         const float4 lo = res.val[(rc * 2 + 0) * 32 + lane], hi = res.val[(rc * 2 + 1) * 32 + lane];
         b.v[0] = __float_as_uint(lo.x); b.v[1] = __float_as_uint(lo.y); b.v[2] = __float_as_uint(lo.z); b.v[3] = __float_as_uint(lo.w);
         b.v[4] = __float_as_uint(hi.x); b.v[5] = __float_as_uint(hi.y); b.v[6] = __float_as_uint(hi.z); b.v[7] = __float_as_uint(hi.w);
-        b.c = res.col[rc * 32 + lane];
+        if (C8) { const uint2 c = reinterpret_cast<const uint2*>(res.col)[rc * 32 + lane]; b.c.x = c.x; b.c.y = c.y; }
+        else b.c = reinterpret_cast<const uint4*>(res.col)[rc * 32 + lane];
         return;
     }
     const float* vp = sp.val + ((size_t)chunk * 32 + lane) * kSpChunk;
-    const uint4* cp = reinterpret_cast<const uint4*>(sp.col) + (size_t)chunk * 32 + lane;
     if (keep > 0) {
         asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
@@ -207,24 +208,47 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
         asm volatile("ld.global.nc.L1::no_allocate.L2::evict_normal.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
     }
-    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                 : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol));
+    if (C8) {
+        const uint2* cp = reinterpret_cast<const uint2*>(sp.col8) + (size_t)chunk * 32 + lane;
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;"
+                     : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol));
+    } else {
+        const uint4* cp = reinterpret_cast<const uint4*>(sp.col) + (size_t)chunk * 32 + lane;
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol));
+    }
 }
 
-// s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]); the offsets are BYTE offsets into it.
-__device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float& acc_hi, float& acc_lo)
+// s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]).
+//   16-bit format: the stream carries BYTE offsets into it.
+//   8-bit format (C8): it carries, per lane, the distance in columns from the lane's previous entry (from column 0 at
+//   the start of a unit; padding repeats the last column); `pos` is the lane's running byte offset.
+template <bool C8>
+__device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float& acc_hi, float& acc_lo, unsigned int& pos)
 {
     const unsigned char* base = reinterpret_cast<const unsigned char*>(s_hl);
-    const unsigned int w[4] = {b.c.x, b.c.y, b.c.z, b.c.w};
+    if (C8) {
+        const unsigned int w[2] = {b.c.x, b.c.y};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const float2 h0 = *reinterpret_cast<const float2*>(base + (w[j] & 0xFFFFu));
-        const float2 h1 = *reinterpret_cast<const float2*>(base + (w[j] >> 16));
-        const float v0 = __uint_as_float(b.v[2 * j]), v1 = __uint_as_float(b.v[2 * j + 1]);
-        acc_hi = __fmaf_rn(v0, h0.x, acc_hi);
-        acc_lo = __fmaf_rn(v0, h0.y, acc_lo);
-        acc_hi = __fmaf_rn(v1, h1.x, acc_hi);
-        acc_lo = __fmaf_rn(v1, h1.y, acc_lo);
+        for (int j = 0; j < 8; ++j) {
+            pos += ((w[j >> 2] >> (8 * (j & 3))) & 0xFFu) << 3;
+            const float2 h = *reinterpret_cast<const float2*>(base + pos);
+            const float v = __uint_as_float(b.v[j]);
+            acc_hi = __fmaf_rn(v, h.x, acc_hi);
+            acc_lo = __fmaf_rn(v, h.y, acc_lo);
+        }
+    } else {
+        const unsigned int w[4] = {b.c.x, b.c.y, b.c.z, b.c.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 h0 = *reinterpret_cast<const float2*>(base + (w[j] & 0xFFFFu));
+            const float2 h1 = *reinterpret_cast<const float2*>(base + (w[j] >> 16));
+            const float v0 = __uint_as_float(b.v[2 * j]), v1 = __uint_as_float(b.v[2 * j + 1]);
+            acc_hi = __fmaf_rn(v0, h0.x, acc_hi);
+            acc_lo = __fmaf_rn(v0, h0.y, acc_lo);
+            acc_hi = __fmaf_rn(v1, h1.x, acc_hi);
+            acc_lo = __fmaf_rn(v1, h1.y, acc_lo);
+        }
     }
 }
 
@@ -303,7 +327,7 @@ struct SpSeqGrid {
 
 // Put the first kSpRing chunks of a sequence in flight (ring slots 0 ..), e.g. for the NEXT iteration while the
 // barrier and the merge of this one run.
-template <class SEQ>
+template <bool C8, class SEQ>
 __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, int lane, uint64_t pol_keep, uint64_t pol_stream)
 {
     SpCursor p;
@@ -312,7 +336,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) {
         if (p.k < seq.k_end) {
-            sp_load(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep > 0 ? pol_keep : pol_stream);
+            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep > 0 ? pol_keep : pol_stream);
             sp_next(p, seq);
         }
     }
@@ -322,7 +346,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 // consumed slot is refilled at once with the chunk kSpRing ahead.  (Measured: rings of 2, 3, 4 and 6 chunks run
 // at the same speed -- the sweep is bound by the shared-memory gathers, not by loads in flight.)  begin(k) runs when a unit starts (row scalars), end(k, dot_hi, dot_lo) after its last chunk, with the
 // G-lane sums done.
-template <int G, class SEQ, class BEGIN, class END>
+template <int G, bool C8, class SEQ, class BEGIN, class END>
 __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, const float2* s_hl, int lane,
                                          uint64_t pol_keep, uint64_t pol_stream, BEGIN begin, END end)
 {
@@ -333,13 +357,14 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) if (prd.k < seq.k_end) sp_next(prd, seq);
     float acc_hi = 0.f, acc_lo = 0.f;
+    unsigned int pos = 0;                    // 8-bit format: this lane's byte offset into s_hl
     bool more = cns.k < seq.k_end;
     while (more) {
 #pragma unroll
         for (int b = 0; b < kSpRing; ++b) {
             if (more) {
-                if (cns.c == 0) begin(cns.k);
-                sp_fma(ring[b], s_hl, acc_hi, acc_lo);
+                if (cns.c == 0) { begin(cns.k); pos = 0; }
+                sp_fma<C8>(ring[b], s_hl, acc_hi, acc_lo, pos);
                 if (cns.c + 1 >= cns.nc) {
                     sp_group_sum<G>(acc_hi, acc_lo);
                     end(cns.k, acc_hi, acc_lo);
@@ -348,7 +373,7 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
                 sp_next(cns, seq);
                 more = cns.k < seq.k_end;
                 if (prd.k < seq.k_end) {
-                    sp_load(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep > 0 ? pol_keep : pol_stream);
+                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep > 0 ? pol_keep : pol_stream);
                     sp_next(prd, seq);
                 }
             }

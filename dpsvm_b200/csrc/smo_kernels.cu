@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_generic_kernel(const
 // in flight; the selected pair sits in shared memory interleaved as (x_hi[c], x_lo[c]) so that one
 // 64-bit shared load serves both dot products of a non-zero.
 // ------------------------------------------------------------------------------------------------
-template <int G>
+template <int G, bool C8>
 __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const PassDev a)
 {
     constexpr int GROUPS = 32 / G;
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
     // the stream does not depend on the pair: first chunks in flight before the dependency wait
     SpBuf ring[kSpRing];
     const SpRes res{0u, 0u, nullptr, nullptr};      // nothing is kept on chip across kernel launches
-    if (a.early_load) sp_prefetch(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
+    if (a.early_load) sp_prefetch<C8>(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
@@ -390,12 +390,12 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
         s_hl[4 * i + 3] = make_float2(h.w, l.w);
     }
     __syncthreads();
-    if (!a.early_load) sp_prefetch(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
+    if (!a.early_load) sp_prefetch<C8>(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
 
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false;
-    sp_sweep<G>(ring, a.sp, res, seq, s_hl, lane, pol_keep, pol_stream,
+    sp_sweep<G, C8>(ring, a.sp, res, seq, s_hl, lane, pol_keep, pol_stream,
         [&](int k) {
             erow = seq.local(k) * GROUPS + grp;
             eown = (sub == 0) && (erow < a.n);
@@ -886,12 +886,21 @@ cudaError_t launch_pass_sparse(const PassDev& a0, int variant, cudaStream_t s)
     if (blocks < 1) blocks = 1;
     a.reverse = variant & 1;
     // same L2 budget as the dense pass: a prefix of the stream is loaded evict_last once it outgrows L2
-    a.sp.pin_steps = (variant & 2) ? (unsigned int)((double)((variant >> 8) & 0xFFFFF) * 1e6 / 192.0) : 0u;
+    a.sp.pin_steps = (variant & 2) ? (unsigned int)((double)((variant >> 8) & 0xFFFFF) * 1e6 / (double)a.sp.step_bytes) : 0u;
+    if (a.sp.col8) {
+        switch (a.sp.lanes) {
+            case 4: return launch_ex(smo_pass_sparse_kernel<4, true>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+            case 8: return launch_ex(smo_pass_sparse_kernel<8, true>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+            case 16: return launch_ex(smo_pass_sparse_kernel<16, true>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+            case 32: return launch_ex(smo_pass_sparse_kernel<32, true>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        }
+        return cudaErrorInvalidValue;
+    }
     switch (a.sp.lanes) {
-        case 4: return launch_ex(smo_pass_sparse_kernel<4>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
-        case 8: return launch_ex(smo_pass_sparse_kernel<8>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
-        case 16: return launch_ex(smo_pass_sparse_kernel<16>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
-        case 32: return launch_ex(smo_pass_sparse_kernel<32>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 4: return launch_ex(smo_pass_sparse_kernel<4, false>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 8: return launch_ex(smo_pass_sparse_kernel<8, false>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 16: return launch_ex(smo_pass_sparse_kernel<16, false>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
+        case 32: return launch_ex(smo_pass_sparse_kernel<32, false>, blocks, kPassThreads, 0, s, a.pdl != 0, a);
     }
     return cudaErrorInvalidValue;
 }

@@ -37,7 +37,12 @@ constexpr int kSpChunk = 8;             // steps per chunk = alignment of a unit
 constexpr int kSpRing = 4;              // register chunks per warp: one being consumed, three in flight (what an HBM-sized stream needs)
 struct SparseDev {
     const float* val;           // null: dense sweep
-    const unsigned short* col;
+    const unsigned short* col;  // 16-bit format: byte offsets 8 * column
+    const unsigned char* col8;  // 8-bit format (null: not in use): per lane, the distance in columns from the lane's previous
+                                // entry (from column 0 at the first step of a unit; padding entries carry 0).  Same chunk
+                                // geometry, col8[(q * 32 + lane) * 8 + i]: one 64-bit load per lane and chunk, 160 instead of
+                                // 192 bytes per step.  Built when no distance exceeds 255 (always so for d <= 256).
+    int step_bytes;             // 192 or 160
     const unsigned int* unit_off;   // [n_units + 1] first step of each unit
     const int* cta_first;       // [grid + 1] first unit of each CTA of the resident loop (balanced by steps)
     // resident loop: which units of its CTA each warp sweeps.  Units differ in length (whole chunks of 8 steps), so the
@@ -264,6 +269,8 @@ cudaError_t launch_sparse_unit_steps(const int* row_nnz, int n, int lanes, unsig
 cudaError_t launch_sparse_scan(const unsigned int* unit_steps, int n_units, unsigned int* unit_off, cudaStream_t s);
 cudaError_t launch_sparse_fill(const float* x, int n, int pitch, int lanes, const unsigned int* unit_off,
                                float* val, unsigned short* col, cudaStream_t s);
+cudaError_t launch_sparse_col8(const float* val, const unsigned short* col, const unsigned int* unit_off, int n_units, unsigned char* col8,
+                               int* too_far, cudaStream_t s);
 cudaError_t launch_sparse_row_norms(const float* val, const unsigned int* unit_off, int n_units, int n, int lanes, float* out, cudaStream_t s);
 
 }  // namespace dpsvm

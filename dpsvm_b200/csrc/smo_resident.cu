@@ -123,7 +123,8 @@ __device__ __forceinline__ int lru_lookup(const LruTable& t, int lines, int k, i
 // SG == 0: the sweep reads the dense rows (LPR lanes per row, ITERS float4 chunks per lane).
 // SG  > 0: the sweep reads the sparse stream with SG lanes per row (SparseDev, smo_kernels.cuh); LPR and
 //          ITERS then only size the two selected-row buffers.  Everything outside the sweep is shared.
-template <int LPR, int ITERS, int SG>
+// C8: the sparse stream carries 8-bit column distances instead of 16-bit offsets (SparseDev::col8).
+template <int LPR, int ITERS, int SG, bool C8 = false>
 __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const ResidentDev a)
 {
     constexpr bool SPARSE = SG > 0;
@@ -146,7 +147,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     unsigned short* s_cnt = s_perm + ((a.sp.perm_stride + 7) & ~7);
     // ... then the first chunks of this CTA's part of the stream, kept on chip for the whole launch
     float4* s_rval = reinterpret_cast<float4*>(s_cnt + 16);
-    uint4* s_rcol = reinterpret_cast<uint4*>(s_rval + (size_t)a.sp.res_chunks * 64);
+    uint2* s_rcol = reinterpret_cast<uint2*>(s_rval + (size_t)a.sp.res_chunks * 64);      // uint4 per lane and chunk in the 16-bit format
     // their per-row scalars live on chip as well (a warp round on a stationary unit then touches no
     // global memory at all): |x|^2, y, f, alpha -- [a.res_units * RPW] each, after the rows
     float* s_rxsq = reinterpret_cast<float*>(s_x + (size_t)a.res_units * RPW * a.pitch4);
@@ -277,12 +278,14 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         sp_res.chunk0 = c_first;
         sp_res.n = min(c_end - c_first, a.sp.res_chunks);
         const float4* gv = reinterpret_cast<const float4*>(a.sp.val) + (size_t)c_first * 64;      // [chunk][lane][2 x float4]
-        const uint4* gc = reinterpret_cast<const uint4*>(a.sp.col) + (size_t)c_first * 32;
+        const int col_u2 = C8 ? 1 : 2;                   // 8-byte words of column data per lane and chunk
+        const uint2* gc = C8 ? reinterpret_cast<const uint2*>(a.sp.col8) + (size_t)c_first * 32
+                             : reinterpret_cast<const uint2*>(a.sp.col) + (size_t)c_first * 64;
         for (unsigned int i = tid; i < sp_res.n * 64u; i += kResThreads) {
             const unsigned int rc = i >> 6, half = (i >> 5) & 1u, ln = i & 31u;
             s_rval[i] = ldg_stream4(gv + (size_t)(rc * 32u + ln) * 2u + half);
         }
-        for (unsigned int i = tid; i < sp_res.n * 32u; i += kResThreads) s_rcol[i] = __ldg(gc + i);
+        for (unsigned int i = tid; i < sp_res.n * 32u * col_u2; i += kResThreads) s_rcol[i] = __ldg(gc + i);
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int i = a.pitch4 + tid; i < CAP4; i += kResThreads) { s_hi[i] = z; s_lo[i] = z; }
     } else {
@@ -550,9 +553,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         } else if constexpr (SPARSE) {
             SpSeqCta& seq = seq_sp;
             seq.rev = rev;
-            if (!pre) sp_prefetch(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
+            if (!pre) sp_prefetch<C8>(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
             pre = false;
-            sp_sweep<SGL>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
+            sp_sweep<SGL, C8>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
                 [&](int k) {
                     erow = (u0 + seq.local(k)) * GROUPS + grp;
                     eown = (sub == 0) && (erow < a.n);
@@ -638,7 +641,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             if constexpr (SPARSE) {
                 if (!last_iter) {
                     seq_sp.rev = !rev;
-                    sp_prefetch(sp_ring, a.sp, sp_res, seq_sp, lane, pol_keep, pol_stream);
+                    sp_prefetch<C8>(sp_ring, a.sp, sp_res, seq_sp, lane, pol_keep, pol_stream);
                     pre = true;
                 }
             } else {
@@ -844,12 +847,13 @@ static cudaError_t launch_resident_lpr(int iters, const ResidentDev& a, int vari
 }
 
 // Sparse sweep: the two selected-row buffers are sized for the widest supported row (LPR 32 x ITERS 8).
-template <int SG>
+template <int SG, bool C8>
 static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStream_t s)
 {
     constexpr int CAP4 = 256;
     static_assert(CAP4 * 4 == kSparseMaxPitch, "selected-row buffers cover the widest sparse row");
-    auto kernel = smo_resident_kernel<32, 8, SG>;
+    auto kernel = smo_resident_kernel<32, 8, SG, C8>;
+    constexpr size_t kChunkBytes = C8 ? 1280 : 1536;         // 32 lanes x 8 steps x (4 + 1 or 2) bytes
     static ResCfg s_cache[kMaxDevices];
     static std::mutex s_mu;
     ResCfg cfg;
@@ -863,20 +867,20 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
     const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int) +
                          (((size_t)a.sp.perm_stride + 7) & ~(size_t)7) * sizeof(unsigned short) + 16 * sizeof(unsigned short);
     if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;
-    // the rest of shared memory holds the head of each CTA's part of the stream (1.5 KB per chunk)
+    // the rest of shared memory holds the head of each CTA's part of the stream (1.25 or 1.5 KB per chunk)
     size_t res_bytes = (size_t)s_smem_max - fixed;
     {
         static const char* cap_env = getenv("DPSVM_SP_RES_KB");      // tuning aid: cap the on-chip part
         if (cap_env && *cap_env) { const size_t cap = (size_t)atoi(cap_env) * 1024; if (cap < res_bytes) res_bytes = cap; }
     }
     const size_t per_cta_chunks = ((size_t)a.sp.total_steps / kSpChunk + s_grid - 1) / s_grid + 64;    // no CTA holds more
-    a.sp.res_chunks = (unsigned int)std::min(res_bytes / 1536, per_cta_chunks);
-    const size_t smem = fixed + (size_t)a.sp.res_chunks * 1536;
+    a.sp.res_chunks = (unsigned int)std::min(res_bytes / kChunkBytes, per_cta_chunks);
+    const size_t smem = fixed + (size_t)a.sp.res_chunks * kChunkBytes;
     a.res_units = 0;
     a.pin_units = 0;
     const bool hint = (variant & 2) != 0;
     a.stream_evict_first = hint ? 1 : 0;
-    a.sp.pin_steps = hint ? (unsigned int)(((double)((variant >> 8) & 0xFFFFF) * 1e6 / s_grid) / 192.0) : 0u;
+    a.sp.pin_steps = hint ? (unsigned int)(((double)((variant >> 8) & 0xFFFFF) * 1e6 / s_grid) / (double)a.sp.step_bytes) : 0u;
     a.parity0 = variant & 1;
     void* args[] = {&a};
     return cudaLaunchCooperativeKernel((void*)kernel, dim3((unsigned)s_grid), dim3(kResThreads), args, smem, s);
@@ -884,11 +888,20 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
 
 cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream_t s)
 {
+    if (a.sp.col8) {
+        switch (a.sp.lanes) {
+            case 4: return launch_resident_sparse_t<4, true>(a, variant, s);
+            case 8: return launch_resident_sparse_t<8, true>(a, variant, s);
+            case 16: return launch_resident_sparse_t<16, true>(a, variant, s);
+            case 32: return launch_resident_sparse_t<32, true>(a, variant, s);
+        }
+        return cudaErrorInvalidValue;
+    }
     switch (a.sp.lanes) {
-        case 4: return launch_resident_sparse_t<4>(a, variant, s);
-        case 8: return launch_resident_sparse_t<8>(a, variant, s);
-        case 16: return launch_resident_sparse_t<16>(a, variant, s);
-        case 32: return launch_resident_sparse_t<32>(a, variant, s);
+        case 4: return launch_resident_sparse_t<4, false>(a, variant, s);
+        case 8: return launch_resident_sparse_t<8, false>(a, variant, s);
+        case 16: return launch_resident_sparse_t<16, false>(a, variant, s);
+        case 32: return launch_resident_sparse_t<32, false>(a, variant, s);
     }
     return cudaErrorInvalidValue;
 }

@@ -232,6 +232,8 @@ CASES = [
     ("mnist_1024_tight", 1e-4, 1e-4, 0, True),
     ("adult_1000_tight", 1e-4, 1e-4, 0, True),
     ("tiny_3x5", 1e-4, 1e-4, 0, False),
+    # above 4 096 rows, optimum pinned: 9 222 iterations of seq.cpp (17 minutes on one core), 3 288 support vectors
+    ("mnist_8192_tight", 1e-4, 1e-4, 0, True),
 ]
 
 
@@ -257,6 +259,25 @@ def test_end_to_end_against_seq_goldens(golden, name, b_tol, alpha_tol, sv_slack
             assert np.array_equal(pred, g["test_labels"])
             assert np.abs(dual - g["test_dual"]).max() < 1e-3
             assert nsv == int((g["alpha"] != 0).sum())
+
+
+@pytest.mark.parametrize("name", ["mnist_512", "adult_2048", "mnist_4096", "odd_d_333x37", "mnist_1024_tight", "adult_1000_tight",
+                                  "mnist_8192_tight"])
+def test_iteration_count_margin_of_both_summation_orders(golden, monkeypatch, name):
+    """How thin the 1 % iteration bound is, stated as a test: the dense and the sparse summation order end within 1 % of
+    EACH OTHER on every golden, and each within 1 % of seq.cpp -- except the one measured case the end-to-end test
+    documents (sparse order forced on the 333 x 37 set, which has no zeros: 1.13 %)."""
+    g = golden(name)
+    ref_it = int(g["num_iter"])
+    its = {}
+    for mode in ("dense", "sparse"):
+        monkeypatch.setenv("DPSVM_LAYOUT", mode)
+        with _trainer(g) as t:
+            its[mode] = t.train().num_iter
+    tol = max(1, int(round(0.01 * ref_it)))
+    assert abs(its["dense"] - ref_it) <= tol, (its, ref_it)
+    assert abs(its["sparse"] - ref_it) <= (max(1, int(round(0.015 * ref_it))) if name == "odd_d_333x37" else tol), (its, ref_it)
+    assert abs(its["dense"] - its["sparse"]) <= (2 * tol if name == "odd_d_333x37" else tol), (its, ref_it)
 
 
 def test_eta_zero_duplicates(golden, layout):
@@ -748,6 +769,50 @@ def test_sparse_stream_edge_rows(monkeypatch):
             a, f[mode], _ = t.download()
             assert np.isfinite(f[mode]).all() and st.num_iter == 80
     assert np.abs(f["dense"] - f["sparse"]).max() < 1e-4
+
+
+def test_sparse_stream_column_formats(golden, monkeypatch):
+    """The stream stores a lane's columns as 8-bit distances from its previous entry (160 bytes per step) when every
+    distance fits, else as 16-bit offsets (192 bytes per step).  Both formats feed the same products to the same
+    accumulators in the same order: results are bit-identical; a gap of more than 255 columns falls back to 16 bits."""
+    monkeypatch.setenv("DPSVM_LAYOUT", "sparse")
+    g = golden("mnist_512")
+    out = {}
+    for cols in ("8", "16"):
+        monkeypatch.setenv("DPSVM_SPARSE_COLS", cols)
+        for flags in (0, capi.FLAG_GRAPH_LOOP):
+            with _trainer(g, cache_size=4, flags=flags) as t:
+                lanes, nnz, sweep = t.layout_info()
+                st = t.train(300)
+                a, f, _ = t.download()
+                out[(cols, flags)] = (sweep, st.num_iter, a, f)
+    ref = out[("16", 0)]
+    assert out[("8", 0)][0] * 192 == ref[0] * 160              # the same steps at 160 instead of 192 bytes
+    for k, v in out.items():
+        assert v[1] == ref[1] and np.array_equal(v[2], ref[2]) and np.array_equal(v[3], ref[3]), k
+    # rows whose two non-zeros are 500 columns apart: the distance does not fit, the offsets stay
+    monkeypatch.delenv("DPSVM_SPARSE_COLS")
+    rng = np.random.default_rng(2)
+    n, d = 256, 600
+    x = np.zeros((n, d), np.float32)
+    x[:, 0] = rng.random(n, dtype=np.float32) + 0.5
+    x[:, 1] = rng.random(n, dtype=np.float32)
+    x[:, 2] = rng.random(n, dtype=np.float32)
+    x[:, 3] = rng.random(n, dtype=np.float32)
+    x[:, 4] = rng.random(n, dtype=np.float32)
+    x[np.arange(n), 500 + (np.arange(n) % 90)] = 1.0
+    y = np.where(rng.random(n) < 0.5, 1, -1).astype(np.int32)
+    res = {}
+    for mode in ("dense", "sparse"):
+        monkeypatch.setenv("DPSVM_LAYOUT", mode)
+        with capi.Trainer(n, d, 5.0, 0.3, 1e-3, cache_size=0) as t:
+            t.upload(x, y)
+            lanes, nnz, sweep = t.layout_info()
+            if mode == "sparse":
+                assert lanes == 4 and nnz == 6 * n and sweep == 192 * 8 * (n // 8)      # one chunk of 8 steps per unit of 8 rows, 16-bit offsets
+            st = t.train(60)
+            res[mode] = t.download()[1]
+    assert np.abs(res["dense"] - res["sparse"]).max() < 1e-4
 
 
 # ------------------------------------------------------------------------------------------------

@@ -19,10 +19,11 @@ def test_port_reproduces_reference_goldens(name, golden, oracle):
     assert r.b == g["b"]
 
 
-def test_port_prefix_of_large_golden(golden, oracle):
-    """mnist_4096 takes minutes on one core: check the first 60 iterations of the trace only."""
-    g = golden("mnist_4096")
-    k = 60
+@pytest.mark.parametrize("name,k", [("mnist_4096", 60), ("mnist_8192_tight", 40)])
+def test_port_prefix_of_large_golden(golden, oracle, name, k):
+    """mnist_4096 and mnist_8192_tight take minutes (17 for the latter) on one core: check the first iterations of the
+    trace only."""
+    g = golden(name)
     r = oracle.train(g["x"], g["y"], float(g["c"]), float(g["gamma"]), float(g["epsilon"]), k,
                      nthreads=oracle.max_threads(), trace_cap=k)
     assert np.array_equal(r.trace_idx, g["trace_idx"][:k])
@@ -32,7 +33,7 @@ def test_port_prefix_of_large_golden(golden, oracle):
 def test_selection_rules_agree_on_goldens(golden, oracle):
     """seq.cpp's set-order scan and the lowest-index rule pick the same pair on these sets
     (the golden files record 0 disagreements); the CUDA path implements the lowest-index rule."""
-    for name in SMALL + ["mnist_4096", "mnist_1024_tight"]:
+    for name in SMALL + ["mnist_4096", "mnist_1024_tight", "mnist_8192_tight"]:
         assert int(golden(name)["rule_disagreements"]) == 0
 
 

@@ -48,7 +48,10 @@ CASES = {
     "odd_d_333x37": ("mnist_like", dict(n=333, d=37, seed=4), 10.0, 0.25, 1e-3, 150000, 0),
     "dups_96x16": ("dups", dict(), 10.0, 0.5, 1e-3, 20000, 0),
     "tiny_3x5": ("mnist_like", dict(n=3, d=5, seed=2), 1.0, 0.25, 1e-3, 1000, 0),
+    # the 1 % iteration bound above 4 096 rows, at a tolerance that pins the optimum (minutes of seq.cpp on one core)
+    "mnist_8192_tight": ("mnist_like", dict(n=8192, d=784, seed=13), 10.0, 0.25, 1e-5, 400000, 256),
 }
+TRACE_CAP = {"mnist_8192_tight": 2048}      # pairs kept in the file (the others keep every iteration)
 
 
 def gen(name, kw):
@@ -83,7 +86,7 @@ def main():
             continue
         x, y = gen(g, kw)
         t = time.time()
-        r = po.ref_train(x, y, c, gamma, eps, max_iter, trace_cap=max_iter)
+        r = po.ref_train(x, y, c, gamma, eps, max_iter, trace_cap=TRACE_CAP.get(name, max_iter))
         dt = time.time() - t
         out = dict(
             generator=g, gen_kwargs=repr(kw), c=np.float32(c), gamma=np.float32(gamma), epsilon=np.float32(eps),
