@@ -100,23 +100,35 @@ struct LruTable {
     int* stamp;    // [lines]
     int* meta;     // [0] = size, [1] = clock
 };
-__device__ __forceinline__ int lru_lookup(const LruTable& t, int lines, int k, int* hit)
+// One lookup by a whole warp (lines <= 64: two table entries per lane): the match is a ballot, the victim of a full table
+// the lane holding the smallest stamp (stamps are distinct).  Same decisions as the serial scan it replaces -- first free
+// line, else least recently used -- in a few dozen cycles instead of a walk over the table by one thread, which sat
+// on the critical path of every iteration (measured: the reference's default 10 lines cost 1.8 us per iteration).
+__device__ __forceinline__ int lru_lookup_warp(const LruTable& t, int lines, int k, int* hit)
 {
+    const int lane = threadIdx.x & 31;
     const int size = t.meta[0];
-    int line = -1;
-    for (int i = 0; i < size; ++i) if (t.key[i] == k) { line = i; break; }
-    *hit = line >= 0;
-    if (line < 0) {
-        if (size < lines) {
-            line = size;
-            t.meta[0] = size + 1;
-        } else {
-            line = 0;
-            for (int i = 1; i < size; ++i) if (t.stamp[i] < t.stamp[line]) line = i;
-        }
-        t.key[line] = k;
+    const bool m0 = lane < size && t.key[lane] == k, m1 = lane + 32 < size && t.key[lane + 32] == k;
+    const unsigned int b0 = __ballot_sync(0xffffffffu, m0), b1 = __ballot_sync(0xffffffffu, m1);
+    int line;
+    *hit = (b0 | b1) != 0u;
+    if (b0 | b1) {
+        line = b0 ? __ffs((int)b0) - 1 : 32 + __ffs((int)b1) - 1;
+    } else if (size < lines) {
+        line = size;
+    } else {
+        const unsigned int s0 = lane < size ? (unsigned int)t.stamp[lane] : 0xffffffffu;
+        const unsigned int s1 = lane + 32 < size ? (unsigned int)t.stamp[lane + 32] : 0xffffffffu;
+        const unsigned int mn = __reduce_min_sync(0xffffffffu, min(s0, s1));
+        const unsigned int v0 = __ballot_sync(0xffffffffu, s0 == mn), v1 = __ballot_sync(0xffffffffu, s1 == mn);
+        line = v0 ? __ffs((int)v0) - 1 : 32 + __ffs((int)v1) - 1;
     }
-    t.stamp[line] = ++t.meta[1];
+    __syncwarp();
+    if (lane == 0) {
+        if (!*hit) { t.key[line] = k; if (size < lines) t.meta[0] = size + 1; }
+        t.stamp[line] = ++t.meta[1];
+    }
+    __syncwarp();
     return line;
 }
 
@@ -162,7 +174,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     __shared__ int s_flag;
     __shared__ int s_lru_key[kResCacheLines], s_lru_stamp[kResCacheLines], s_lru_meta[2];
     __shared__ float s_delta[4];                       // delta_hi, delta_lo, alpha_hi_new, alpha_lo_new of this iteration
-    __shared__ struct { int both_hit; float* line_hi; float* line_lo; float xsq_hi, xsq_lo; } s_early;   // known before eta
+    __shared__ struct { int both_hit; int hits; float* line_hi; float* line_lo; float xsq_hi, xsq_lo; } s_early;   // known before eta
     __shared__ unsigned int s_ll[kMaxPeers * kLLWords];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -408,33 +420,42 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             y_hi = __ldg(a.y + r_hi); y_lo = __ldg(a.y + r_lo);
             xsq_hi = __ldg(a.xsq + r_hi); xsq_lo = __ldg(a.xsq + r_lo);
         }
-        if (tid == 0) {
-            int both = 0;
-            float* l_hi_p = nullptr;
-            float* l_lo_p = nullptr;
-            if (a.cache_direct) {
+        if (a.cache_direct) {
+            if (tid == 0) {
                 float* p_hi = a.cache_data + (size_t)i_hi * a.line_stride;
                 float* p_lo = a.cache_data + (size_t)i_lo * a.line_stride;
+                float* l_hi_p = nullptr;
+                float* l_lo_p = nullptr;
+                int both = 0;
                 if (hit_hi && hit_lo) { both = 1; l_hi_p = p_hi; l_lo_p = p_lo; }
                 else { if (!hit_hi) l_hi_p = p_hi; if (!hit_lo) l_lo_p = p_lo; }
-            } else if (a.cache_lines > 0) {
+                s_early.both_hit = both; s_early.line_hi = l_hi_p; s_early.line_lo = l_lo_p; s_early.hits = hit_hi + hit_lo;
+                if (cta == 0 && !both) {
+                    if (!hit_hi) a.cache_stamp[i_hi] = num_iter + 1;
+                    if (!hit_lo) a.cache_stamp[i_lo] = num_iter + 1;
+                    __threadfence();        // ordered before this thread's slot store, which is what the other CTAs wait for
+                }
+            }
+        } else if (a.cache_lines > 0) {
+            if (warp == 1) {                // a whole warp per lookup, off thread 0's path (it is issuing the row copies)
                 LruTable t{s_lru_key, s_lru_stamp, s_lru_meta};
-                const int l_hi = lru_lookup(t, a.cache_lines, i_hi, &hit_hi);      // hi then lo (svmTrain.cu:203,238)
-                const int l_lo = lru_lookup(t, a.cache_lines, i_lo, &hit_lo);
-                float* p_hi = a.cache_data + (size_t)l_hi * a.line_stride;
-                float* p_lo = a.cache_data + (size_t)l_lo * a.line_stride;
-                if (hit_hi && hit_lo) { both = 1; l_hi_p = p_hi; l_lo_p = p_lo; }
-                else { if (!hit_hi) l_hi_p = p_hi; if (!hit_lo && l_lo != l_hi) l_lo_p = p_lo; }
+                const int l_hi = lru_lookup_warp(t, a.cache_lines, i_hi, &hit_hi);      // hi then lo (svmTrain.cu:203,238)
+                const int l_lo = lru_lookup_warp(t, a.cache_lines, i_lo, &hit_lo);
+                if (lane == 0) {
+                    float* p_hi = a.cache_data + (size_t)l_hi * a.line_stride;
+                    float* p_lo = a.cache_data + (size_t)l_lo * a.line_stride;
+                    float* l_hi_p = nullptr;
+                    float* l_lo_p = nullptr;
+                    int both = 0;
+                    if (hit_hi && hit_lo) { both = 1; l_hi_p = p_hi; l_lo_p = p_lo; }
+                    else { if (!hit_hi) l_hi_p = p_hi; if (!hit_lo && l_lo != l_hi) l_lo_p = p_lo; }
+                    s_early.both_hit = both; s_early.line_hi = l_hi_p; s_early.line_lo = l_lo_p; s_early.hits = hit_hi + hit_lo;
+                }
             }
-            s_early.both_hit = both; s_early.line_hi = l_hi_p; s_early.line_lo = l_lo_p;
-            s_early.xsq_hi = xsq_hi; s_early.xsq_lo = xsq_lo;
-            if (a.cache_lines > 0) { cache_lookups += 2; cache_hits += hit_hi + hit_lo; }
-            if (a.cache_direct && cta == 0 && !(hit_hi && hit_lo)) {
-                if (!hit_hi) a.cache_stamp[i_hi] = num_iter + 1;
-                if (!hit_lo) a.cache_stamp[i_lo] = num_iter + 1;
-                __threadfence();        // ordered before this thread's slot store, which is what the other CTAs wait for
-            }
+        } else if (tid == 0) {
+            s_early.both_hit = 0; s_early.line_hi = nullptr; s_early.line_lo = nullptr; s_early.hits = 0;
         }
+        if (tid == 0) { s_early.xsq_hi = xsq_hi; s_early.xsq_lo = xsq_lo; }
         if (a.world > 1 && !ll_mode) __syncthreads();
         else mbar_wait(&s_bar, (uint32_t)(it & 1));
         stamp(it, 1);
@@ -463,6 +484,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         bool have_deltas = false;
         if (warp == 0) {
             if (tid == 0) {
+                if (a.cache_lines > 0) { cache_lookups += 2; cache_hits += s_early.hits; }
                 float norm_sq = 0.f;
 #pragma unroll
                 for (int w = 0; w < kCtlThreads / 32; ++w) norm_sq = __fadd_rn(norm_sq, s_part[w]);

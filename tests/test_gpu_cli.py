@@ -96,3 +96,32 @@ def test_reference_gpu_path_rebuilt_for_sm100_agrees(case):
     it, b, nsv, acc, _ = _run(REFGPU, g, "train.csv", "model_rg.txt", extra=["-s", "10"])
     ref_it = int(g["num_iter"])
     assert abs(it - ref_it) <= round(0.03 * ref_it) and abs(b - float(g["b"])) < 2e-3
+
+
+def test_bench_line_carries_the_contract_and_matches_the_reference_arm(tmp_path):
+    """bench.py on a reduced row count (seconds): one JSON line with every key the driver reads, and a `config` object
+    identical to the one `--impl reference` prints for the same arguments (the driver compares the two arms' configs)."""
+    import json
+    import sys
+    common = ["--rows", "6000", "--steps", "3", "--warmup", "3"]
+    ours = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--e2e-steps", "1", "--converge", "1", "--no-cpu-baseline",
+                           "--no-ref-gpu"] + common, capture_output=True, text=True, timeout=600)
+    assert ours.returncode == 0, ours.stderr[-3000:]
+    d = json.loads([l for l in ours.stdout.splitlines() if l.startswith("{")][-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "roofline", "e2e", "time_to_converge", "gpu_launches", "clocks"):
+        assert key in d, key
+    assert d["metric"] == "smo_iterations_per_s" and d["unit"] == "iter/s" and d["value"] > 0 and d["gpu_launches"] > 0
+    for key in ("bound", "achieved", "peak", "unit", "frac", "traffic", "frac_dense_basis"):
+        assert key in d["roofline"], key
+    assert abs(d["roofline"]["frac"] - d["roofline"]["achieved"] / d["roofline"]["peak"]) < 1e-9
+    assert d["e2e"]["h2d_bytes_per_step"] == 4 * 6000 * 784 + 4 * 6000 and d["e2e"]["value"] > 0
+    ttc = d["time_to_converge"]
+    assert ttc["converged"] is True and ttc["iterations"] > 0 and ttc["n_sv"] > 0 and ttc["seconds"] > 0
+    big = d["time_to_converge_hbm_cache"]
+    assert big["same_result_as_small_cache"] is True and big["loop"] == "resident" and 0 < big["cache_hit_rate"] < 1
+    ref = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference"] + common,
+                         capture_output=True, text=True, timeout=600)
+    assert ref.returncode == 0, ref.stderr[-2000:]
+    r = json.loads([l for l in ref.stdout.splitlines() if l.startswith("{")][-1])
+    assert r["config"] == d["config"] and r["metric"] == d["metric"] and r["unit"] == d["unit"]
