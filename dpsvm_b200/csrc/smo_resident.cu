@@ -508,9 +508,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                     st->num_iter = num_iter + 1;
                     st->cache_hits = cache_hits; st->cache_lookups = cache_lookups;
                 }
-                __threadfence_block();
             }
             __syncwarp();
+            // (no fence: when a named barrier completes, what its arriving threads wrote before is visible to the threads it releases)
             asm volatile("bar.arrive 1, %0;" ::"n"(kResThreads) : "memory");
             have_deltas = true;
         }
