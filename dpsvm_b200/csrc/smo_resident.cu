@@ -577,19 +577,38 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             seq.rev = rev;
             if (!pre) sp_prefetch<C8>(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
             pre = false;
+            // Per-row epilogues are batched: a finished unit leaves one (dot_hi, dot_lo) pair per row in the G lanes of that
+            // row's group, i.e. GROUPS = 32 / G results in a warp.  Running the epilogue there would keep GROUPS of 32
+            // lanes busy for ~200 instructions per unit (measured: a fifth of the sweep's instruction stream).  Instead
+            // lane L parks the result of group L % GROUPS of the (L / GROUPS)-th unit since the last flush -- and requests
+            // that row's scalars -- and after G units every lane holds one row: ONE epilogue pass with all lanes active.
+            // Same values, same stores; the candidate minima are order-independent (distinct keys).
+            int unit_row0 = 0, n_parked = 0;
+            int p_row = -1;
+            float p_dh = 0.f, p_dl = 0.f;
+            auto flush = [&]() {
+                need_deltas();
+                if (p_row >= 0) epilogue(p_row, p_dh, p_dl, e_xsq, e_f, e_alpha, e_y, true);
+                p_row = -1;
+                n_parked = 0;
+            };
             sp_sweep<SGL, C8>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
-                [&](int k) {
-                    erow = (u0 + seq.local(k)) * GROUPS + grp;
-                    eown = (sub == 0) && (erow < a.n);
-                    if (eown) {
-                        e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow);
-                        e_f = a.f[erow]; e_alpha = a.alpha[erow];
-                    }
-                },
+                [&](int k) { unit_row0 = (u0 + seq.local(k)) * GROUPS; },
                 [&](int, float dh, float dl) {
-                    need_deltas();
-                    if (eown) epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, true);
+                    // after the xor-butterfly every lane of a group holds the group's two sums: read group L % GROUPS
+                    const int src = (lane % GROUPS) * SGL;
+                    const float vh = __shfl_sync(0xffffffffu, dh, src), vl = __shfl_sync(0xffffffffu, dl, src);
+                    if (lane / GROUPS == n_parked) {
+                        const int row = unit_row0 + lane % GROUPS;
+                        if (row < a.n) {
+                            p_row = row; p_dh = vh; p_dl = vl;
+                            e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
+                            e_f = a.f[row]; e_alpha = a.alpha[row];
+                        }
+                    }
+                    if (++n_parked == SGL) flush();
                 });
+            flush();
         } else {
             for (int k = wslot; k < my_units; k += NW) {
                 if (!pre) load_const(k, rev);
