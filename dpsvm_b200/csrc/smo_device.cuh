@@ -197,15 +197,16 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
         else b.c = reinterpret_cast<const uint4*>(res.col)[rc * 32 + lane];
         return;
     }
+    // Two policies: keep (evict_last) for what should stay in L2 from one iteration to the next -- all of a stream that
+    // fits, else its pinned prefix -- and evict_first for the rest of a stream that does not fit.  (keep < 0, "no hints",
+    // is a stream small enough not to care: kept.)  The 256-bit value loads carry the policy in the opcode; narrower
+    // loads cannot (ptxas), they take the policy register the caller selected.
     const float* vp = sp.val + ((size_t)chunk * 32 + lane) * kSpChunk;
-    if (keep > 0) {
+    if (keep != 0) {
         asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
-    } else if (keep == 0) {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
     } else {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_normal.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
     }
     if (C8) {
@@ -228,11 +229,17 @@ __device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float
 {
     const unsigned char* base = reinterpret_cast<const unsigned char*>(s_hl);
     if (C8) {
+        // `pos` is a 32-bit shared-memory ADDRESS here (it starts at s_hl's own address at the first step of a unit): per
+        // entry one byte permute, one multiply-add and the load -- left to itself the compiler builds a longer
+        // shift / mask / add tree and adds the base separately
         const unsigned int w[2] = {b.c.x, b.c.y};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            pos += ((w[j >> 2] >> (8 * (j & 3))) & 0xFFu) << 3;
-            const float2 h = *reinterpret_cast<const float2*>(base + pos);
+            unsigned int dist;
+            asm("prmt.b32 %0, %1, 0, %2;" : "=r"(dist) : "r"(w[j >> 2]), "r"(0x4440u | (unsigned int)(j & 3)));
+            asm("mad.lo.u32 %0, %1, 8, %0;" : "+r"(pos) : "r"(dist));
+            float2 h;
+            asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(h.x), "=f"(h.y) : "r"(pos));
             const float v = __uint_as_float(b.v[j]);
             acc_hi = __fmaf_rn(v, h.x, acc_hi);
             acc_lo = __fmaf_rn(v, h.y, acc_lo);
@@ -336,7 +343,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) {
         if (p.k < seq.k_end) {
-            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep > 0 ? pol_keep : pol_stream);
+            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep != 0 ? pol_keep : pol_stream);
             sp_next(p, seq);
         }
     }
@@ -357,13 +364,14 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) if (prd.k < seq.k_end) sp_next(prd, seq);
     float acc_hi = 0.f, acc_lo = 0.f;
-    unsigned int pos = 0;                    // 8-bit format: this lane's byte offset into s_hl
+    const unsigned int pos0 = C8 ? smem_u32(s_hl) : 0u;
+    unsigned int pos = pos0;                 // 8-bit format: the shared-memory address of this lane's current column in s_hl
     bool more = cns.k < seq.k_end;
     while (more) {
 #pragma unroll
         for (int b = 0; b < kSpRing; ++b) {
             if (more) {
-                if (cns.c == 0) { begin(cns.k); pos = 0; }
+                if (cns.c == 0) { begin(cns.k); pos = pos0; }
                 sp_fma<C8>(ring[b], s_hl, acc_hi, acc_lo, pos);
                 if (cns.c + 1 >= cns.nc) {
                     sp_group_sum<G>(acc_hi, acc_lo);
@@ -373,7 +381,7 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
                 sp_next(cns, seq);
                 more = cns.k < seq.k_end;
                 if (prd.k < seq.k_end) {
-                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep > 0 ? pol_keep : pol_stream);
+                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep != 0 ? pol_keep : pol_stream);
                     sp_next(prd, seq);
                 }
             }

@@ -339,7 +339,14 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     const int my_units = u1 - u0;
     const int n_stream = my_units - res_units;
     float4 xv[R][ITERS];
-    SpBuf sp_ring[kSpRing];                            // sparse: the chunks in flight
+    SpBuf sp_ring[kSpRing];                            // sparse: the chunks in flight ...
+    unsigned int sp_tag[kSpRing];                      // ... each with its unit's first row | kTagFirst | kTagLast
+    int sp_n_prod = 0;                                 // chunks requested so far in the current sequence
+    // the ONE cursor of the sparse sweep: where the next chunk to REQUEST is (unit pj of this warp slot's list, chunk pc of
+    // its pnc); the consumer needs no cursor of its own, a chunk's tag says where its unit starts and ends
+    int sp_pj = 0, sp_pc = 0, sp_pnc = 0, sp_pkeep = 0, sp_cnt = 0;
+    unsigned int sp_pchunk0 = 0, sp_prow0 = 0;
+    bool sp_prev = false;
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false, pre = false, unit_in_smem = false;
@@ -556,15 +563,36 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const bool keep_going = b_lo > __fadd_rn(b_hi, __fmul_rn(2.0f, a.epsilon));
         const bool last_iter = !keep_going || (num_iter + 1) >= a.max_iter || (num_iter + 1) >= stop_at || (it + 1) >= a.chunk;
 
-        SpSeqCta seq_sp;                    // this warp's units in the sparse stream (unused by the dense sweep)
-        if constexpr (SPARSE) {
-            seq_sp.k_first = 0; seq_sp.k_stride = 1; seq_sp.k_end = (int)s_cnt[wslot];
-            seq_sp.uoff = s_uoff;
-            seq_sp.perm = s_perm + wslot; seq_sp.perm_step = NW;
-            seq_sp.rev = rev;
-            seq_sp.hint = a.stream_evict_first;
-            seq_sp.pin_steps = a.sp.pin_steps;
-        }
+        // ---- sparse sweep: request side (SparseDev::perm: the units of this warp slot, first steps in shared memory) ----
+        constexpr unsigned int kTagFirst = 1u << 30, kTagLast = 1u << 31, kTagRow = (1u << 30) - 1u;
+        auto sp_open = [&]() {                       // cursor -> unit sp_pj of the list, in the cursor's direction
+            const int lu = (int)s_perm[(sp_prev ? (sp_cnt - 1 - sp_pj) : sp_pj) * NW + wslot];
+            const unsigned int beg = s_uoff[lu];
+            sp_pnc = (int)(s_uoff[lu + 1] - beg) / kSpChunk;
+            sp_pchunk0 = beg / kSpChunk;
+            sp_pkeep = a.stream_evict_first ? ((beg - s_uoff[0]) < a.sp.pin_steps ? 1 : 0) : -1;
+            sp_prow0 = (unsigned int)((u0 + lu) * GROUPS);
+            sp_pc = 0;
+        };
+        auto sp_start = [&](bool direction) {        // a new sequence: nothing requested yet
+            sp_prev = direction;
+            sp_cnt = (int)s_cnt[wslot];
+            sp_pj = 0; sp_n_prod = 0;
+            if (sp_cnt > 0) sp_open();
+        };
+        auto sp_request = [&](int b) {               // next chunk of the sequence -> ring slot b (no-op once the list is exhausted)
+            if (sp_pj < sp_cnt) {
+                sp_tag[b] = sp_prow0 | (sp_pc == 0 ? kTagFirst : 0u) | (sp_pc + 1 == sp_pnc ? kTagLast : 0u);
+                sp_load<C8>(sp_ring[b], a.sp, sp_res, sp_pchunk0 + (unsigned int)sp_pc, lane, sp_pkeep, sp_pkeep != 0 ? pol_keep : pol_stream);
+                ++sp_n_prod;
+                if (++sp_pc == sp_pnc) { if (++sp_pj < sp_cnt) sp_open(); }
+            }
+        };
+        auto sp_prime = [&](bool direction) {        // first kSpRing chunks of a sequence in flight
+            sp_start(direction);
+#pragma unroll
+            for (int b = 0; b < kSpRing; ++b) sp_request(b);
+        };
         if (both_hit) {
             // both kernel rows cached: no X, 28 B per row
             need_deltas();
@@ -573,9 +601,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             for (int row = row_b + tid; row < row_e; row += kResThreads)
                 epilogue(row, s_early.line_hi[row], s_early.line_lo[row], __ldg(a.xsq + row), a.f[row], a.alpha[row], __ldg(a.y + row), false);
         } else if constexpr (SPARSE) {
-            SpSeqCta& seq = seq_sp;
-            seq.rev = rev;
-            if (!pre) sp_prefetch<C8>(sp_ring, a.sp, sp_res, seq, lane, pol_keep, pol_stream);
+            if (!pre) sp_prime(rev);
             pre = false;
             // Per-row epilogues are batched: a finished unit leaves one (dot_hi, dot_lo) pair per row in the G lanes of that
             // row's group, i.e. GROUPS = 32 / G results in a warp.  Running the epilogue there would keep GROUPS of 32
@@ -592,22 +618,40 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 p_row = -1;
                 n_parked = 0;
             };
-            sp_sweep<SGL, C8>(sp_ring, a.sp, sp_res, seq, s_hl, lane, pol_keep, pol_stream,
-                [&](int k) { unit_row0 = (u0 + seq.local(k)) * GROUPS; },
-                [&](int, float dh, float dl) {
-                    // after the xor-butterfly every lane of a group holds the group's two sums: read group L % GROUPS
-                    const int src = (lane % GROUPS) * SGL;
-                    const float vh = __shfl_sync(0xffffffffu, dh, src), vl = __shfl_sync(0xffffffffu, dl, src);
-                    if (lane / GROUPS == n_parked) {
-                        const int row = unit_row0 + lane % GROUPS;
-                        if (row < a.n) {
-                            p_row = row; p_dh = vh; p_dl = vl;
-                            e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
-                            e_f = a.f[row]; e_alpha = a.alpha[row];
+            {
+                const unsigned int pos0 = C8 ? smem_u32(s_hl) : 0u;
+                unsigned int pos = pos0;         // 8-bit format: shared-memory address of this lane's current column in s_hl
+                float acc_hi = 0.f, acc_lo = 0.f;
+                int n_cons = 0;
+                while (n_cons < sp_n_prod) {
+#pragma unroll
+                    for (int b = 0; b < kSpRing; ++b) {
+                        if (n_cons < sp_n_prod) {
+                            const unsigned int tag = sp_tag[b];
+                            if (tag & kTagFirst) { unit_row0 = (int)(tag & kTagRow); pos = pos0; }
+                            sp_fma<C8>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
+                            ++n_cons;
+                            sp_request(b);       // the consumed slot takes the chunk kSpRing ahead at once
+                            if (tag & kTagLast) {
+                                sp_group_sum<SGL>(acc_hi, acc_lo);
+                                // after the xor-butterfly every lane of a group holds the group's two sums: read group L % GROUPS
+                                const int src = (lane % GROUPS) * SGL;
+                                const float vh = __shfl_sync(0xffffffffu, acc_hi, src), vl = __shfl_sync(0xffffffffu, acc_lo, src);
+                                if (lane / GROUPS == n_parked) {
+                                    const int row = unit_row0 + lane % GROUPS;
+                                    if (row < a.n) {
+                                        p_row = row; p_dh = vh; p_dl = vl;
+                                        e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
+                                        e_f = a.f[row]; e_alpha = a.alpha[row];
+                                    }
+                                }
+                                if (++n_parked == SGL) flush();
+                                acc_hi = 0.f; acc_lo = 0.f;
+                            }
                         }
                     }
-                    if (++n_parked == SGL) flush();
-                });
+                }
+            }
             flush();
         } else {
             for (int k = wslot; k < my_units; k += NW) {
@@ -681,8 +725,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         auto prefetch_next = [&]() {
             if constexpr (SPARSE) {
                 if (!last_iter) {
-                    seq_sp.rev = !rev;
-                    sp_prefetch<C8>(sp_ring, a.sp, sp_res, seq_sp, lane, pol_keep, pol_stream);
+                    sp_prime(!rev);
                     pre = true;
                 }
             } else {
