@@ -186,7 +186,7 @@ struct SpRes {
 };
 
 template <bool C8>
-__device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpRes& res, unsigned int chunk, int lane, int keep, uint64_t pol)
+__device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpRes& res, unsigned int chunk, int lane, int keep, uint64_t pol_keep, uint64_t pol_stream)
 {
     const unsigned int rc = chunk - res.chunk0;
     if (rc < res.n) {
@@ -202,21 +202,21 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
     // is a stream small enough not to care: kept.)  The 256-bit value loads carry the policy in the opcode; narrower
     // loads cannot (ptxas), they take the policy register the caller selected.
     const float* vp = sp.val + ((size_t)chunk * 32 + lane) * kSpChunk;
+    const void* cp = C8 ? static_cast<const void*>(reinterpret_cast<const uint2*>(sp.col8) + (size_t)chunk * 32 + lane)
+                        : static_cast<const void*>(reinterpret_cast<const uint4*>(sp.col) + (size_t)chunk * 32 + lane);
+    // (the policy register stays uniform inside each branch: no per-thread select, no move to a uniform register per load)
     if (keep != 0) {
         asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+        if (C8) asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;" : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol_keep));
+        else asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                          : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol_keep));
     } else {
         asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
-    }
-    if (C8) {
-        const uint2* cp = reinterpret_cast<const uint2*>(sp.col8) + (size_t)chunk * 32 + lane;
-        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;"
-                     : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol));
-    } else {
-        const uint4* cp = reinterpret_cast<const uint4*>(sp.col) + (size_t)chunk * 32 + lane;
-        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-                     : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol));
+        if (C8) asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;" : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol_stream));
+        else asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                          : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol_stream));
     }
 }
 
@@ -343,7 +343,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) {
         if (p.k < seq.k_end) {
-            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, p.keep != 0 ? pol_keep : pol_stream);
+            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, pol_keep, pol_stream);
             sp_next(p, seq);
         }
     }
@@ -381,7 +381,7 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
                 sp_next(cns, seq);
                 more = cns.k < seq.k_end;
                 if (prd.k < seq.k_end) {
-                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, prd.keep != 0 ? pol_keep : pol_stream);
+                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, pol_keep, pol_stream);
                     sp_next(prd, seq);
                 }
             }

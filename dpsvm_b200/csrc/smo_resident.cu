@@ -583,7 +583,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         auto sp_request = [&](int b) {               // next chunk of the sequence -> ring slot b (no-op once the list is exhausted)
             if (sp_pj < sp_cnt) {
                 sp_tag[b] = sp_prow0 | (sp_pc == 0 ? kTagFirst : 0u) | (sp_pc + 1 == sp_pnc ? kTagLast : 0u);
-                sp_load<C8>(sp_ring[b], a.sp, sp_res, sp_pchunk0 + (unsigned int)sp_pc, lane, sp_pkeep, sp_pkeep != 0 ? pol_keep : pol_stream);
+                sp_load<C8>(sp_ring[b], a.sp, sp_res, sp_pchunk0 + (unsigned int)sp_pc, lane, sp_pkeep, pol_keep, pol_stream);
                 ++sp_n_prod;
                 if (++sp_pc == sp_pnc) { if (++sp_pj < sp_cnt) sp_open(); }
             }
