@@ -350,6 +350,8 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false, pre = false, unit_in_smem = false;
+    int unit_first_row = 0;                            // dense sweep: first row of the unit whose X is in xv
+    (void)eown; (void)erow;
     // constants of the k-th unit of this warp's sequence: streamed units first (forward or reverse),
     // the shared-memory slice last (it fills the tail while the slower SMs finish streaming)
     auto load_const = [&](int k, bool rv) {
@@ -357,12 +359,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         unit_in_smem = in_smem;
         const int u = in_smem ? (u0 + (k - n_stream)) : (rv ? (u1 - 1 - k) : (us0 + k));
         const int row0 = u * RPW + grp * R;
-        erow = row0 + sub;
-        eown = (sub < R) && (erow < a.n);
-        if (eown) {
-            if (in_smem) { e_xsq = s_rxsq[erow - u0 * RPW]; e_y = s_ry[erow - u0 * RPW]; }
-            else { e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow); }
-        }
+        unit_first_row = u * RPW;
         if (in_smem) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -654,13 +651,23 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             }
             flush();
         } else {
+            // Per-row epilogues are batched as in the sparse sweep: a finished unit leaves RPW = (32 / LPR) * R results in a
+            // warp (two for rows of 784 floats); lane L parks result L % RPW of the (L / RPW)-th unit since the last flush and
+            // requests that row's scalars; after 32 / RPW units every lane holds one row and the epilogue runs once, all lanes busy.
+            constexpr int BATCH = 32 / RPW;
+            int n_parked = 0, p_row = -1;
+            float p_dh = 0.f, p_dl = 0.f;
+            auto flush = [&]() {
+                need_deltas();
+                if (p_row >= 0) epilogue(p_row, p_dh, p_dl, e_xsq, e_f, e_alpha, e_y, true);
+                p_row = -1;
+                n_parked = 0;
+            };
             for (int k = wslot; k < my_units; k += NW) {
                 if (!pre) load_const(k, rev);
                 pre = false;
-                if (eown) {                      // state written by the previous iteration / this prologue
-                    if (unit_in_smem) { e_f = s_rf[erow - u0 * RPW]; e_alpha = s_ralpha[erow - u0 * RPW]; }
-                    else { e_f = a.f[erow]; e_alpha = a.alpha[erow]; }
-                }
+                const int this_first_row = unit_first_row;
+                const bool this_in_smem = unit_in_smem;
                 float acc_hi[R], acc_lo[R];
 #pragma unroll
                 for (int r = 0; r < R; ++r) { acc_hi[r] = 0.f; acc_lo[r] = 0.f; }
@@ -685,14 +692,32 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                         acc_lo[r] = __fadd_rn(acc_lo[r], __shfl_xor_sync(0xffffffffu, acc_lo[r], off));
                     }
                 }
-                need_deltas();
-                if (eown) {
-                    float dh = acc_hi[0], dl = acc_lo[0];
+                // every lane of a group now holds the group's R pairs of sums: result q of the unit is row (q / R)'s group, its r = q % R
+                {
+                    const int q = lane % RPW, src = (q / R) * LPR;
+                    float vh = 0.f, vl = 0.f;
 #pragma unroll
-                    for (int r = 1; r < R; ++r) if (sub == r) { dh = acc_hi[r]; dl = acc_lo[r]; }
-                    epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, true);
+                    for (int r = 0; r < R; ++r) {
+                        const float th = __shfl_sync(0xffffffffu, acc_hi[r], src), tl = __shfl_sync(0xffffffffu, acc_lo[r], src);
+                        if (q % R == r) { vh = th; vl = tl; }
+                    }
+                    if (lane / RPW == n_parked) {
+                        const int row = this_first_row + q;
+                        if (row < a.n) {
+                            p_row = row; p_dh = vh; p_dl = vl;
+                            if (this_in_smem) {      // state written by the previous iteration / this prologue
+                                const int li = row - u0 * RPW;
+                                e_xsq = s_rxsq[li]; e_y = s_ry[li]; e_f = s_rf[li]; e_alpha = s_ralpha[li];
+                            } else {
+                                e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
+                                e_f = a.f[row]; e_alpha = a.alpha[row];
+                            }
+                        }
+                    }
+                    if (++n_parked == BATCH) flush();
                 }
             }
+            flush();
         }
         need_deltas();          // a warp without rows this iteration still takes part in the hand-over
         // ================= block best -> slot; all slots -> next pair =================
