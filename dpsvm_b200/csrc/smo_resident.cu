@@ -351,7 +351,6 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     int e_y = 0, erow = 0;
     bool eown = false, pre = false, unit_in_smem = false;
     int unit_first_row = 0;                            // dense sweep: first row of the unit whose X is in xv
-    (void)eown; (void)erow;
     // constants of the k-th unit of this warp's sequence: streamed units first (forward or reverse),
     // the shared-memory slice last (it fills the tail while the slower SMs finish streaming)
     auto load_const = [&](int k, bool rv) {
@@ -360,6 +359,14 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const int u = in_smem ? (u0 + (k - n_stream)) : (rv ? (u1 - 1 - k) : (us0 + k));
         const int row0 = u * RPW + grp * R;
         unit_first_row = u * RPW;
+        if constexpr (RPW > 4) {             // geometries whose epilogue runs per unit (see the dense sweep)
+            erow = row0 + sub;
+            eown = (sub < R) && (erow < a.n);
+            if (eown) {
+                if (in_smem) { e_xsq = s_rxsq[erow - u0 * RPW]; e_y = s_ry[erow - u0 * RPW]; }
+                else { e_xsq = __ldg(a.xsq + erow); e_y = __ldg(a.y + erow); }
+            }
+        }
         if (in_smem) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
@@ -651,6 +658,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             }
             flush();
         } else {
+            if constexpr (RPW <= 4) {
             // Per-row epilogues are batched as in the sparse sweep: a finished unit leaves RPW = (32 / LPR) * R results in a
             // warp (two for rows of 784 floats); lane L parks result L % RPW of the (L / RPW)-th unit since the last flush and
             // requests that row's scalars; after 32 / RPW units every lane holds one row and the epilogue runs once, all lanes busy.
@@ -718,6 +726,49 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 }
             }
             flush();
+            } else {
+                // narrow rows (8 or 16 rows per unit, as many lanes busy in the epilogue): epilogue per unit, its row scalars
+                // requested together with the unit's X (measured at 4 000 000 x 128, HBM-bound: batching costs 5 % there)
+            for (int k = wslot; k < my_units; k += NW) {
+                if (!pre) load_const(k, rev);
+                pre = false;
+                if (eown) {                      // state written by the previous iteration / this prologue
+                    if (unit_in_smem) { e_f = s_rf[erow - u0 * RPW]; e_alpha = s_ralpha[erow - u0 * RPW]; }
+                    else { e_f = a.f[erow]; e_alpha = a.alpha[erow]; }
+                }
+                float acc_hi[R], acc_lo[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) { acc_hi[r] = 0.f; acc_lo[r] = 0.f; }
+#pragma unroll
+                for (int itc = 0; itc < ITERS; ++itc) {
+                    const float4 h = s_hi[sub + itc * LPR];
+                    const float4 l = s_lo[sub + itc * LPR];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const float4 v = xv[r][itc];
+                        acc_hi[r] = __fmaf_rn(v.x, h.x, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.x, l.x, acc_lo[r]);
+                        acc_hi[r] = __fmaf_rn(v.y, h.y, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.y, l.y, acc_lo[r]);
+                        acc_hi[r] = __fmaf_rn(v.z, h.z, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.z, l.z, acc_lo[r]);
+                        acc_hi[r] = __fmaf_rn(v.w, h.w, acc_hi[r]); acc_lo[r] = __fmaf_rn(v.w, l.w, acc_lo[r]);
+                    }
+                }
+#pragma unroll
+                for (int off = LPR / 2; off >= 1; off >>= 1) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        acc_hi[r] = __fadd_rn(acc_hi[r], __shfl_xor_sync(0xffffffffu, acc_hi[r], off));
+                        acc_lo[r] = __fadd_rn(acc_lo[r], __shfl_xor_sync(0xffffffffu, acc_lo[r], off));
+                    }
+                }
+                need_deltas();
+                if (eown) {
+                    float dh = acc_hi[0], dl = acc_lo[0];
+#pragma unroll
+                    for (int r = 1; r < R; ++r) if (sub == r) { dh = acc_hi[r]; dl = acc_lo[r]; }
+                    epilogue(erow, dh, dl, e_xsq, e_f, e_alpha, e_y, true);
+                }
+            }
+            }
         }
         need_deltas();          // a warp without rows this iteration still takes part in the hand-over
         // ================= block best -> slot; all slots -> next pair =================
