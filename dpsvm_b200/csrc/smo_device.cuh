@@ -224,7 +224,10 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
 //   16-bit format: the stream carries BYTE offsets into it.
 //   8-bit format (C8): it carries, per lane, the distance in columns from the lane's previous entry (from column 0 at
 //   the start of a unit; padding repeats the last column); `pos` is the lane's running byte offset.
-template <bool C8>
+// REP = 4: the pair is replicated sixteen times, s_rep[col][16] float2 (128 bytes per column), and s_hl / pos point at THIS
+// lane's copy, s_rep[0][lane & 15]: lane l of a half-warp only ever touches bank pair l, so every 64-bit gather is free of
+// bank conflicts whatever the columns are (REP = 0: the plain interleaved row, sixteen random columns collide on 16 bank pairs).
+template <bool C8, int REP = 0>
 __device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float& acc_hi, float& acc_lo, unsigned int& pos)
 {
     const unsigned char* base = reinterpret_cast<const unsigned char*>(s_hl);
@@ -237,7 +240,7 @@ __device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float
         for (int j = 0; j < 8; ++j) {
             unsigned int dist;
             asm("prmt.b32 %0, %1, 0, %2;" : "=r"(dist) : "r"(w[j >> 2]), "r"(0x4440u | (unsigned int)(j & 3)));
-            asm("mad.lo.u32 %0, %1, 8, %0;" : "+r"(pos) : "r"(dist));
+            asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(pos) : "r"(dist), "n"(8 << REP));
             float2 h;
             asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(h.x), "=f"(h.y) : "r"(pos));
             const float v = __uint_as_float(b.v[j]);
@@ -248,8 +251,8 @@ __device__ __forceinline__ void sp_fma(const SpBuf& b, const float2* s_hl, float
         const unsigned int w[4] = {b.c.x, b.c.y, b.c.z, b.c.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float2 h0 = *reinterpret_cast<const float2*>(base + (w[j] & 0xFFFFu));
-            const float2 h1 = *reinterpret_cast<const float2*>(base + (w[j] >> 16));
+            const float2 h0 = *reinterpret_cast<const float2*>(base + ((w[j] & 0xFFFFu) << REP));
+            const float2 h1 = *reinterpret_cast<const float2*>(base + ((w[j] >> 16) << REP));
             const float v0 = __uint_as_float(b.v[2 * j]), v1 = __uint_as_float(b.v[2 * j + 1]);
             acc_hi = __fmaf_rn(v0, h0.x, acc_hi);
             acc_lo = __fmaf_rn(v0, h0.y, acc_lo);

@@ -152,8 +152,10 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     float4* s_lo = s_hi + CAP4;
     float4* s_x = s_lo + CAP4;                         // dense: stationary rows [res_units * RPW][pitch4]
     // sparse: the pair interleaved, (x_hi[c], x_lo[c]), then the first step of each of this CTA's units
-    float2* s_hl = reinterpret_cast<float2*>(s_lo + CAP4);
-    unsigned int* s_uoff = reinterpret_cast<unsigned int*>(s_hl + CAP4 * 4);
+    // (sixteen copies of it, s_rep[column][16], so that the sweep's gathers are free of bank conflicts: sp_fma<., 4>)
+    float4* s_rep = s_lo + CAP4;
+    const float2* s_hl = reinterpret_cast<const float2*>(reinterpret_cast<const unsigned char*>(s_rep) + (threadIdx.x & 15) * 8);   // this lane's copy
+    unsigned int* s_uoff = reinterpret_cast<unsigned int*>(s_rep + (size_t)a.pitch4 * 4 * 8);
     // ... the units each warp slot sweeps (SparseDev::perm, cnt) ...
     unsigned short* s_perm = reinterpret_cast<unsigned short*>(s_uoff + ((a.sp.max_cta_units + 1 + 3) & ~3));
     unsigned short* s_cnt = s_perm + ((a.sp.perm_stride + 7) & ~7);
@@ -478,13 +480,22 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             float part = 0.f;
             for (int i = tid; i < a.pitch4 * 4; i += kCtlThreads) {
                 const float vh = fh[i], vl = fl[i];
-                if (SPARSE) s_hl[i] = make_float2(vh, vl);
                 const float df = __fsub_rn(vh, vl);
                 part = __fmaf_rn(df, df, part);
             }
 #pragma unroll
             for (int off = 16; off >= 1; off >>= 1) part = __fadd_rn(part, __shfl_xor_sync(0xffffffffu, part, off));
             if (lane == 0) s_part[warp] = part;
+        }
+        if constexpr (SPARSE) {
+            // the pair, interleaved and replicated: 8 x 16 bytes per column, by all threads
+            const float* fh = reinterpret_cast<const float*>(s_hi);
+            const float* fl = reinterpret_cast<const float*>(s_lo);
+            for (int i = tid; i < a.pitch4 * 4 * 8; i += kResThreads) {
+                const int col = i >> 3;
+                const float vh = fh[col], vl = fl[col];
+                s_rep[i] = make_float4(vh, vl, vh, vl);
+            }
         }
         __syncthreads();
         stamp(it, 2);
@@ -633,7 +644,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                         if (n_cons < sp_n_prod) {
                             const unsigned int tag = sp_tag[b];
                             if (tag & kTagFirst) { unit_row0 = (int)(tag & kTagRow); pos = pos0; }
-                            sp_fma<C8>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
+                            sp_fma<C8, 4>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
                             ++n_cons;
                             sp_request(b);       // the consumed slot takes the chunk kSpRing ahead at once
                             if (tag & kTagLast) {
@@ -1024,7 +1035,7 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
     const int s_smem_max = cfg.smem_max, s_grid = cfg.grid;
     if (a.sp.grid != s_grid) return cudaErrorInvalidValue;      // cta_first was balanced for another grid
     static_assert(kResThreads / 32 == 16, "SparseDev::perm deals the units of a CTA to 16 warp slots");
-    const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)CAP4 * 4 * sizeof(float2) + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int) +
+    const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)a.pitch4 * 4 * 128 + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int) +
                          (((size_t)a.sp.perm_stride + 7) & ~(size_t)7) * sizeof(unsigned short) + 16 * sizeof(unsigned short);
     if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;
     // the rest of shared memory holds the head of each CTA's part of the stream (1.25 or 1.5 KB per chunk)
