@@ -272,6 +272,8 @@ __device__ __forceinline__ void sp_group_sum(float& acc_hi, float& acc_lo)
     }
 }
 
+// (The resident loop's sparse sweep walks its units with one cursor and a tag per chunk in flight, smo_resident.cu; the
+// cursor pair below serves the graph loop's pass kernel.)
 // A warp's position in its chunk sequence: sequence unit k (k_first, k_first + k_stride, ... < k_end), chunk c of
 // the unit's nc chunks.  SEQ supplies  void unit(int k, unsigned int& first_step, int& steps)  and the L2 policy
 // int keep(unsigned int first_step).
@@ -299,25 +301,6 @@ __device__ __forceinline__ void sp_next(SpCursor& q, const SEQ& seq)
     if (++q.c >= q.nc) { q.k += seq.k_stride; sp_open(q, seq); }
 }
 
-// Resident loop: the units one warp slot sweeps in its CTA (SparseDev::perm), first steps in shared memory, forward
-// or reverse.  Sequence index k = 0 .. k_end - 1 runs over the slot's list.
-struct SpSeqCta {
-    int k_first, k_stride, k_end;       // 0, 1, units of this slot
-    const unsigned int* uoff;           // [units of the CTA + 1] in shared memory
-    const unsigned short* perm;         // this slot's first entry; consecutive entries are perm_step apart
-    int perm_step;
-    bool rev;
-    int hint;                           // 0: no eviction hints at all
-    unsigned int pin_steps;             // steps of the CTA's range (from its start) kept in L2
-    __device__ __forceinline__ int local(int k) const { return (int)perm[(rev ? (k_end - 1 - k) : k) * perm_step]; }
-    __device__ __forceinline__ void unit(int k, unsigned int& beg, int& steps) const
-    {
-        const int lu = local(k);
-        beg = uoff[lu];
-        steps = (int)(uoff[lu + 1] - beg);
-    }
-    __device__ __forceinline__ int keep(unsigned int beg) const { return hint ? ((beg - uoff[0]) < pin_steps ? 1 : 0) : -1; }
-};
 // Graph loop: units of the whole shard, first steps in global memory.
 struct SpSeqGrid {
     int k_first, k_stride, k_end;       // k_end = units of the shard
