@@ -562,6 +562,35 @@ def test_resident_and_graph_loops_are_bit_identical(golden, name, cache, layout)
     assert np.array_equal(r[6], q[6]) and np.array_equal(r[7], q[7]) and r[8] == q[8]
 
 
+@pytest.mark.parametrize("n,d,mode", [(700, 200, "dense"), (900, 300, "dense"), (600, 520, "dense"), (640, 1000, "dense"),
+                                      (900, 300, "sparse"), (640, 1000, "sparse"), (1500, 60, "sparse")])
+def test_resident_and_graph_loops_agree_for_every_row_geometry(monkeypatch, n, d, mode):
+    """The goldens are 784, 123, 37, 16 and 5 columns wide.  The resident loop has one instantiation per row geometry
+    (4, 8, 16 or 32 lanes per row; epilogues batched for rows of more than 256 floats, per unit below; the sparse sweep's
+    replicated pair up to 1 024 columns): random rows of the other widths, both loops, bit-identical after 300 iterations,
+    and f against a float64 evaluation from the downloaded alpha."""
+    monkeypatch.setenv("DPSVM_LAYOUT", mode)
+    rng = np.random.default_rng(n + d)
+    x = (rng.random((n, d), dtype=np.float32) < 0.3).astype(np.float32) * rng.random((n, d), dtype=np.float32)
+    y = np.where(rng.random(n) < 0.5, 1, -1).astype(np.int32)
+    gamma = 2.0 / d
+    out = []
+    for flags in (0, capi.FLAG_GRAPH_LOOP):
+        with capi.Trainer(n, d, 5.0, gamma, 1e-3, cache_size=6, flags=flags) as t:
+            t.upload(x, y)
+            assert t.loop_info()[0] is (flags == 0)
+            st = t.train(300)
+            a, f, _ = t.download()
+            out.append((st.num_iter, st.cache_hits, a, f))
+    assert out[0][:2] == out[1][:2] and np.array_equal(out[0][2], out[1][2]) and np.array_equal(out[0][3], out[1][3])
+    alpha, f = out[0][2], out[0][3]
+    x64 = x.astype(np.float64)
+    sv = np.flatnonzero(alpha)
+    d2 = ((x64[:, None, :] - x64[None, sv, :]) ** 2).sum(-1)
+    want = np.exp(-gamma * d2) @ (alpha[sv].astype(np.float64) * y[sv]) - y
+    assert np.abs(f - want).max() < 300 * F_TOL
+
+
 def test_loops_can_be_mixed_with_the_dropin_steps(golden, layout):
     """resident chunks, then host-directed train_step2 iterations (split kernels), then resident again:
     the kernel-row cache is emptied at each switch, results are those of an uninterrupted run."""
