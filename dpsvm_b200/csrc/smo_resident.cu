@@ -487,8 +487,9 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             for (int off = 16; off >= 1; off >>= 1) part = __fadd_rn(part, __shfl_xor_sync(0xffffffffu, part, off));
             if (lane == 0) s_part[warp] = part;
         }
-        if constexpr (SPARSE) {
-            // the pair, interleaved and replicated: 8 x 16 bytes per column, by all threads
+        if (SPARSE && !(a.cache_direct && hit_hi && hit_lo)) {
+            // the pair, interleaved and replicated: 8 x 16 bytes per column, by all threads (not when both kernel rows are
+            // cached: that iteration has no sweep; with a line per row every thread knows the two hits for itself)
             const float* fh = reinterpret_cast<const float*>(s_hi);
             const float* fl = reinterpret_cast<const float*>(s_lo);
             for (int i = tid; i < a.pitch4 * 4 * 8; i += kResThreads) {
