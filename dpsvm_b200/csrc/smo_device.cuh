@@ -220,6 +220,54 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
     }
 }
 
+// The resident loop's form of sp_load.  A chunk is named by `o`, THIS LANE's byte offset into the 8-bit column array,
+// (chunk * 32 + lane) * 8: the lane's values sit at 4 * o and its 16-bit column offsets at 2 * o, so that the request side
+// carries one running 32-bit number (+256 per chunk) instead of rebuilding two 64-bit addresses from a chunk index
+// (kSpMaxStepsO bounds the stream so that it fits).  The shared-memory head is the window [o0, o0 + on) of the same offsets.
+// KEEP_ALL: the whole stream fits in L2 -- one value load (evict_last in its opcode) and an unhinted column load, no
+// policy registers; otherwise the two policies of sp_load.
+struct SpResO {
+    unsigned int o0, on;
+    const unsigned char* val;    // [chunk][half][lane] float4
+    const unsigned char* col;    // [chunk][lane] uint2 (8-bit distances) or uint4 (16-bit offsets)
+};
+template <bool C8, bool KEEP_ALL>
+__device__ __forceinline__ void sp_load_at(SpBuf& b, const SparseDev& sp, const SpResO& res, unsigned int o, int lane, int keep, uint64_t pol_keep, uint64_t pol_stream)
+{
+    const unsigned int ro = o - res.o0;
+    if (ro < res.on) {
+        // ro = rc * 256 + lane * 8  ->  values at rc * 1024 + half * 512 + lane * 16 = 4 * ro - 16 * lane (+ 512)
+        const unsigned char* vp = res.val + (4u * ro - 16u * (unsigned int)lane);
+        const uint4 lo = *reinterpret_cast<const uint4*>(vp), hi = *reinterpret_cast<const uint4*>(vp + 512);
+        b.v[0] = lo.x; b.v[1] = lo.y; b.v[2] = lo.z; b.v[3] = lo.w;
+        b.v[4] = hi.x; b.v[5] = hi.y; b.v[6] = hi.z; b.v[7] = hi.w;
+        if (C8) { const uint2 c = *reinterpret_cast<const uint2*>(res.col + ro); b.c.x = c.x; b.c.y = c.y; }
+        else b.c = *reinterpret_cast<const uint4*>(res.col + 2u * ro);
+        return;
+    }
+    const unsigned char* vp = reinterpret_cast<const unsigned char*>(sp.val) + (size_t)o * 4u;
+    const unsigned char* cp = C8 ? reinterpret_cast<const unsigned char*>(sp.col8) + o
+                                 : reinterpret_cast<const unsigned char*>(sp.col) + (size_t)o * 2u;
+    if (KEEP_ALL || keep != 0) {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+        if (KEEP_ALL) {
+            if (C8) asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp));
+            else asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp));
+        } else {
+            if (C8) asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;" : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol_keep));
+            else asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                              : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol_keep));
+        }
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(b.v[0]), "=r"(b.v[1]), "=r"(b.v[2]), "=r"(b.v[3]), "=r"(b.v[4]), "=r"(b.v[5]), "=r"(b.v[6]), "=r"(b.v[7]) : "l"(vp));
+        if (C8) asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0,%1}, [%2], %3;" : "=r"(b.c.x), "=r"(b.c.y) : "l"(cp), "l"(pol_stream));
+        else asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                          : "=r"(b.c.x), "=r"(b.c.y), "=r"(b.c.z), "=r"(b.c.w) : "l"(cp), "l"(pol_stream));
+    }
+}
+
 // s_hl: the selected pair interleaved, s_hl[col] = (x_hi[col], x_lo[col]).
 //   16-bit format: the stream carries BYTE offsets into it.
 //   8-bit format (C8): it carries, per lane, the distance in columns from the lane's previous entry (from column 0 at

@@ -35,6 +35,7 @@ struct PushDev;
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpChunk = 8;             // steps per chunk = alignment of a unit's step count
 constexpr int kSpRing = 4;              // register chunks per warp: one being consumed, three in flight (what an HBM-sized stream needs)
+constexpr unsigned int kSpMaxStepsO = 1u << 27;   // steps of a stream the resident loop's 32-bit lane offsets (sp_load_at) can address: 32 bytes of column distances per step
 struct SparseDev {
     const float* val;           // null: dense sweep
     const unsigned short* col;  // 16-bit format: byte offsets 8 * column

@@ -136,7 +136,7 @@ __device__ __forceinline__ int lru_lookup_warp(const LruTable& t, int lines, int
 // SG  > 0: the sweep reads the sparse stream with SG lanes per row (SparseDev, smo_kernels.cuh); LPR and
 //          ITERS then only size the two selected-row buffers.  Everything outside the sweep is shared.
 // C8: the sparse stream carries 8-bit column distances instead of 16-bit offsets (SparseDev::col8).
-template <int LPR, int ITERS, int SG, bool C8 = false>
+template <int LPR, int ITERS, int SG, bool C8 = false, bool KEEP_ALL = false>
 __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const ResidentDev a)
 {
     constexpr bool SPARSE = SG > 0;
@@ -283,23 +283,24 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         a_hi_old = a.alpha[i_hi - a.index_base];
         a_lo_old = a.alpha[i_lo - a.index_base];
     }
-    SpRes sp_res{0u, 0u, s_rval, s_rcol};
+    SpResO sp_res{0u, 0u, reinterpret_cast<const unsigned char*>(s_rval), reinterpret_cast<const unsigned char*>(s_rcol)};
     if (SPARSE) {
         for (int i = tid; i <= u1 - u0; i += kResThreads) s_uoff[i] = a.sp.unit_off[u0 + i];
         for (int i = tid; i < a.sp.perm_stride; i += kResThreads) s_perm[i] = a.sp.perm[(size_t)cta * a.sp.perm_stride + i];
         if (tid < NW) s_cnt[tid] = a.sp.cnt[cta * NW + tid];
         const unsigned int c_first = a.sp.unit_off[u0] / kSpChunk, c_end = a.sp.unit_off[u1] / kSpChunk;
-        sp_res.chunk0 = c_first;
-        sp_res.n = min(c_end - c_first, a.sp.res_chunks);
+        const unsigned int res_n = min(c_end - c_first, a.sp.res_chunks);
+        sp_res.o0 = c_first * 256u;                      // offsets as sp_load_at counts them: 256 per chunk
+        sp_res.on = res_n * 256u;
         const float4* gv = reinterpret_cast<const float4*>(a.sp.val) + (size_t)c_first * 64;      // [chunk][lane][2 x float4]
         const int col_u2 = C8 ? 1 : 2;                   // 8-byte words of column data per lane and chunk
         const uint2* gc = C8 ? reinterpret_cast<const uint2*>(a.sp.col8) + (size_t)c_first * 32
                              : reinterpret_cast<const uint2*>(a.sp.col) + (size_t)c_first * 64;
-        for (unsigned int i = tid; i < sp_res.n * 64u; i += kResThreads) {
+        for (unsigned int i = tid; i < res_n * 64u; i += kResThreads) {
             const unsigned int rc = i >> 6, half = (i >> 5) & 1u, ln = i & 31u;
             s_rval[i] = ldg_stream4(gv + (size_t)(rc * 32u + ln) * 2u + half);
         }
-        for (unsigned int i = tid; i < sp_res.n * 32u * col_u2; i += kResThreads) s_rcol[i] = __ldg(gc + i);
+        for (unsigned int i = tid; i < res_n * 32u * col_u2; i += kResThreads) s_rcol[i] = __ldg(gc + i);
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int i = a.pitch4 + tid; i < CAP4; i += kResThreads) { s_hi[i] = z; s_lo[i] = z; }
     } else {
@@ -344,10 +345,11 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     SpBuf sp_ring[kSpRing];                            // sparse: the chunks in flight ...
     unsigned int sp_tag[kSpRing];                      // ... each with its unit's first row | kTagFirst | kTagLast
     int sp_n_prod = 0;                                 // chunks requested so far in the current sequence
-    // the ONE cursor of the sparse sweep: where the next chunk to REQUEST is (unit pj of this warp slot's list, chunk pc of
-    // its pnc); the consumer needs no cursor of its own, a chunk's tag says where its unit starts and ends
-    int sp_pj = 0, sp_pc = 0, sp_pnc = 0, sp_pkeep = 0, sp_cnt = 0;
-    unsigned int sp_pchunk0 = 0, sp_prow0 = 0;
+    // the ONE cursor of the sparse sweep: where the next chunk to REQUEST is (unit pj of this warp slot's list, sp_left of
+    // its chunks to go, the next one at this lane's offset sp_po, see sp_load_at); the consumer needs no cursor of its own,
+    // a chunk's tag says where its unit starts and ends
+    int sp_pj = 0, sp_left = 0, sp_pkeep = 0, sp_cnt = 0;
+    unsigned int sp_po = 0, sp_utag = 0;
     bool sp_prev = false;
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
@@ -584,11 +586,10 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         auto sp_open = [&]() {                       // cursor -> unit sp_pj of the list, in the cursor's direction
             const int lu = (int)s_perm[(sp_prev ? (sp_cnt - 1 - sp_pj) : sp_pj) * NW + wslot];
             const unsigned int beg = s_uoff[lu];
-            sp_pnc = (int)(s_uoff[lu + 1] - beg) / kSpChunk;
-            sp_pchunk0 = beg / kSpChunk;
-            sp_pkeep = a.stream_evict_first ? ((beg - s_uoff[0]) < a.sp.pin_steps ? 1 : 0) : -1;
-            sp_prow0 = (unsigned int)((u0 + lu) * GROUPS);
-            sp_pc = 0;
+            sp_left = (int)(s_uoff[lu + 1] - beg) / kSpChunk;
+            sp_po = beg * 32u + (unsigned int)lane * 8u;                 // chunk beg / 8, 256 bytes of column distances per chunk
+            if (!KEEP_ALL) sp_pkeep = a.stream_evict_first ? ((beg - s_uoff[0]) < a.sp.pin_steps ? 1 : 0) : -1;
+            sp_utag = (unsigned int)((u0 + lu) * GROUPS) | kTagFirst;
         };
         auto sp_start = [&](bool direction) {        // a new sequence: nothing requested yet
             sp_prev = direction;
@@ -598,10 +599,13 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         };
         auto sp_request = [&](int b) {               // next chunk of the sequence -> ring slot b (no-op once the list is exhausted)
             if (sp_pj < sp_cnt) {
-                sp_tag[b] = sp_prow0 | (sp_pc == 0 ? kTagFirst : 0u) | (sp_pc + 1 == sp_pnc ? kTagLast : 0u);
-                sp_load<C8>(sp_ring[b], a.sp, sp_res, sp_pchunk0 + (unsigned int)sp_pc, lane, sp_pkeep, pol_keep, pol_stream);
+                const bool last = --sp_left == 0;
+                sp_tag[b] = last ? (sp_utag | kTagLast) : sp_utag;
+                sp_utag &= ~kTagFirst;
+                sp_load_at<C8, KEEP_ALL>(sp_ring[b], a.sp, sp_res, sp_po, lane, sp_pkeep, pol_keep, pol_stream);
+                sp_po += 256u;
                 ++sp_n_prod;
-                if (++sp_pc == sp_pnc) { if (++sp_pj < sp_cnt) sp_open(); }
+                if (last) { if (++sp_pj < sp_cnt) sp_open(); }
             }
         };
         auto sp_prime = [&](bool direction) {        // first kSpRing chunks of a sequence in flight
@@ -635,7 +639,8 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 n_parked = 0;
             };
             {
-                const unsigned int pos0 = C8 ? smem_u32(s_hl) : 0u;
+                unsigned int pos0 = C8 ? smem_u32(s_hl) : 0u;
+                asm volatile("" : "+r"(pos0));   // held in a register: rebuilt from the CTA's shared window it costs a special-register read per chunk
                 unsigned int pos = pos0;         // 8-bit format: shared-memory address of this lane's current column in s_hl
                 float acc_hi = 0.f, acc_lo = 0.f;
                 int n_cons = 0;
@@ -1019,12 +1024,12 @@ static cudaError_t launch_resident_lpr(int iters, const ResidentDev& a, int vari
 }
 
 // Sparse sweep: the two selected-row buffers are sized for the widest supported row (LPR 32 x ITERS 8).
-template <int SG, bool C8>
-static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStream_t s)
+template <int SG, bool C8, bool KEEP_ALL>
+static cudaError_t launch_resident_sparse_k(ResidentDev a, int variant, cudaStream_t s)
 {
     constexpr int CAP4 = 256;
     static_assert(CAP4 * 4 == kSparseMaxPitch, "selected-row buffers cover the widest sparse row");
-    auto kernel = smo_resident_kernel<32, 8, SG, C8>;
+    auto kernel = smo_resident_kernel<32, 8, SG, C8, KEEP_ALL>;
     constexpr size_t kChunkBytes = C8 ? 1280 : 1536;         // 32 lanes x 8 steps x (4 + 1 or 2) bytes
     static ResCfg s_cache[kMaxDevices];
     static std::mutex s_mu;
@@ -1056,6 +1061,18 @@ static cudaError_t launch_resident_sparse_t(ResidentDev a, int variant, cudaStre
     a.parity0 = variant & 1;
     void* args[] = {&a};
     return cudaLaunchCooperativeKernel((void*)kernel, dim3((unsigned)s_grid), dim3(kResThreads), args, smem, s);
+}
+
+// A stream that fits in L2 is kept there as a whole (variant bit 1 clear): the sweep then needs neither the second
+// eviction policy nor the per-unit choice between the two -- KEEP_ALL, built for the lane counts the layout picks
+// by itself (4 and 8; 16 and 32 exist for DPSVM_SPARSE_LANES only).
+template <int SG, bool C8>
+static cudaError_t launch_resident_sparse_t(const ResidentDev& a, int variant, cudaStream_t s)
+{
+    if constexpr (SG <= 8) {
+        if (!(variant & 2)) return launch_resident_sparse_k<SG, C8, true>(a, variant, s);
+    }
+    return launch_resident_sparse_k<SG, C8, false>(a, variant, s);
 }
 
 cudaError_t launch_resident_sparse(const ResidentDev& a, int variant, cudaStream_t s)

@@ -375,10 +375,12 @@ int sparse_setup(dpsvm_ctx* c)
     CU(cudaStreamSynchronize(s));
     const unsigned int total_steps = h_off[n_units];
     const double stream_bytes = 192.0 * (double)total_steps;
-    if (mode == 0 && stream_bytes > kSparseAutoRatio * dense_bytes) {
+    if (mode == 0 && (stream_bytes > kSparseAutoRatio * dense_bytes || total_steps >= kSpMaxStepsO)) {
         CU(dense_norms());
         return DPSVM_OK;
     }
+    if (total_steps >= kSpMaxStepsO)
+        return fail(DPSVM_ERR_LIMIT, "sparse layout: %u steps of 32 non-zeros in this shard, the sweep addresses fewer than %u", total_steps, kSpMaxStepsO);
     const size_t val_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(float));
     const size_t col_bytes = std::max<size_t>(256, (size_t)total_steps * 32 * sizeof(unsigned short));
     CU(grow(c->d_sp_val, c->sp_val_cap, val_bytes));
