@@ -33,6 +33,7 @@
 #include <mutex>
 #include <math.h>
 #include <stdlib.h>
+#include <type_traits>
 
 #include "smo_device.cuh"
 
@@ -343,11 +344,19 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     const int n_stream = my_units - res_units;
     float4 xv[R][ITERS];
     SpBuf sp_ring[kSpRing];                            // sparse: the chunks in flight ...
-    unsigned int sp_tag[kSpRing];                      // ... each with its unit's first row | kTagFirst | kTagLast
-    int sp_n_prod = 0;                                 // chunks requested so far in the current sequence
+    unsigned int sp_tag[kSpRing];                      // ... each with a tag: the unit's first row | kTagLast on a unit's last chunk, else 0
+    int sp_total = 0;                                  // chunks in this warp slot's sequence (the same in every iteration)
+    if (SPARSE) {
+        const int cnt = (int)s_cnt[wslot];
+        for (int j = lane; j < cnt; j += 32) {
+            const int lu = (int)s_perm[j * NW + wslot];
+            sp_total += (int)(s_uoff[lu + 1] - s_uoff[lu]) / kSpChunk;
+        }
+        sp_total = __reduce_add_sync(0xffffffffu, sp_total);
+    }
     // the ONE cursor of the sparse sweep: where the next chunk to REQUEST is (unit pj of this warp slot's list, sp_left of
     // its chunks to go, the next one at this lane's offset sp_po, see sp_load_at); the consumer needs no cursor of its own,
-    // a chunk's tag says where its unit starts and ends
+    // a chunk's tag says where its unit ends (and which rows it was)
     int sp_pj = 0, sp_left = 0, sp_pkeep = 0, sp_cnt = 0;
     unsigned int sp_po = 0, sp_utag = 0;
     bool sp_prev = false;
@@ -582,29 +591,27 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         const bool last_iter = !keep_going || (num_iter + 1) >= a.max_iter || (num_iter + 1) >= stop_at || (it + 1) >= a.chunk;
 
         // ---- sparse sweep: request side (SparseDev::perm: the units of this warp slot, first steps in shared memory) ----
-        constexpr unsigned int kTagFirst = 1u << 30, kTagLast = 1u << 31, kTagRow = (1u << 30) - 1u;
+        constexpr unsigned int kTagLast = 1u << 31, kTagRow = kTagLast - 1u;     // tag of a unit's last chunk: its first row | kTagLast; other chunks: 0
         auto sp_open = [&]() {                       // cursor -> unit sp_pj of the list, in the cursor's direction
             const int lu = (int)s_perm[(sp_prev ? (sp_cnt - 1 - sp_pj) : sp_pj) * NW + wslot];
             const unsigned int beg = s_uoff[lu];
             sp_left = (int)(s_uoff[lu + 1] - beg) / kSpChunk;
             sp_po = beg * 32u + (unsigned int)lane * 8u;                 // chunk beg / 8, 256 bytes of column distances per chunk
             if (!KEEP_ALL) sp_pkeep = a.stream_evict_first ? ((beg - s_uoff[0]) < a.sp.pin_steps ? 1 : 0) : -1;
-            sp_utag = (unsigned int)((u0 + lu) * GROUPS) | kTagFirst;
+            sp_utag = (unsigned int)((u0 + lu) * GROUPS) | kTagLast;
         };
         auto sp_start = [&](bool direction) {        // a new sequence: nothing requested yet
             sp_prev = direction;
             sp_cnt = (int)s_cnt[wslot];
-            sp_pj = 0; sp_n_prod = 0;
+            sp_pj = 0;
             if (sp_cnt > 0) sp_open();
         };
         auto sp_request = [&](int b) {               // next chunk of the sequence -> ring slot b (no-op once the list is exhausted)
             if (sp_pj < sp_cnt) {
                 const bool last = --sp_left == 0;
-                sp_tag[b] = last ? (sp_utag | kTagLast) : sp_utag;
-                sp_utag &= ~kTagFirst;
+                sp_tag[b] = last ? sp_utag : 0u;
                 sp_load_at<C8, KEEP_ALL>(sp_ring[b], a.sp, sp_res, sp_po, lane, sp_pkeep, pol_keep, pol_stream);
                 sp_po += 256u;
-                ++sp_n_prod;
                 if (last) { if (++sp_pj < sp_cnt) sp_open(); }
             }
         };
@@ -629,7 +636,7 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             // lane L parks the result of group L % GROUPS of the (L / GROUPS)-th unit since the last flush -- and requests
             // that row's scalars -- and after G units every lane holds one row: ONE epilogue pass with all lanes active.
             // Same values, same stores; the candidate minima are order-independent (distinct keys).
-            int unit_row0 = 0, n_parked = 0;
+            int n_parked = 0;
             int p_row = -1;
             float p_dh = 0.f, p_dl = 0.f;
             auto flush = [&]() {
@@ -643,34 +650,39 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 asm volatile("" : "+r"(pos0));   // held in a register: rebuilt from the CTA's shared window it costs a special-register read per chunk
                 unsigned int pos = pos0;         // 8-bit format: shared-memory address of this lane's current column in s_hl
                 float acc_hi = 0.f, acc_lo = 0.f;
-                int n_cons = 0;
-                while (n_cons < sp_n_prod) {
-#pragma unroll
-                    for (int b = 0; b < kSpRing; ++b) {
-                        if (n_cons < sp_n_prod) {
-                            const unsigned int tag = sp_tag[b];
-                            if (tag & kTagFirst) { unit_row0 = (int)(tag & kTagRow); pos = pos0; }
-                            sp_fma<C8, 4>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
-                            ++n_cons;
-                            sp_request(b);       // the consumed slot takes the chunk kSpRing ahead at once
-                            if (tag & kTagLast) {
-                                sp_group_sum<SGL>(acc_hi, acc_lo);
-                                // after the xor-butterfly every lane of a group holds the group's two sums: read group L % GROUPS
-                                const int src = (lane % GROUPS) * SGL;
-                                const float vh = __shfl_sync(0xffffffffu, acc_hi, src), vl = __shfl_sync(0xffffffffu, acc_lo, src);
-                                if (lane / GROUPS == n_parked) {
-                                    const int row = unit_row0 + lane % GROUPS;
-                                    if (row < a.n) {
-                                        p_row = row; p_dh = vh; p_dl = vl;
-                                        e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
-                                        e_f = a.f[row]; e_alpha = a.alpha[row];
-                                    }
-                                }
-                                if (++n_parked == SGL) flush();
-                                acc_hi = 0.f; acc_lo = 0.f;
+                auto consume = [&](auto slot) {
+                    constexpr int b = decltype(slot)::value;
+                    const unsigned int tag = sp_tag[b];
+                    sp_fma<C8, 4>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
+                    sp_request(b);               // the consumed slot takes the chunk kSpRing ahead at once
+                    if (tag & kTagLast) {
+                        const int unit_row0 = (int)(tag & kTagRow);
+                        sp_group_sum<SGL>(acc_hi, acc_lo);
+                        // after the xor-butterfly every lane of a group holds the group's two sums: read group L % GROUPS
+                        const int src = (lane % GROUPS) * SGL;
+                        const float vh = __shfl_sync(0xffffffffu, acc_hi, src), vl = __shfl_sync(0xffffffffu, acc_lo, src);
+                        if (lane / GROUPS == n_parked) {
+                            const int row = unit_row0 + lane % GROUPS;
+                            if (row < a.n) {
+                                p_row = row; p_dh = vh; p_dl = vl;
+                                e_xsq = __ldg(a.xsq + row); e_y = __ldg(a.y + row);
+                                e_f = a.f[row]; e_alpha = a.alpha[row];
                             }
                         }
+                        if (++n_parked == SGL) flush();
+                        acc_hi = 0.f; acc_lo = 0.f;
+                        pos = pos0;              // the next chunk starts a unit: column distances count from column 0 again
                     }
+                };
+                // whole rounds of the ring without a per-chunk end test, then the up to three chunks left
+                static_assert(kSpRing == 4, "the sweep is unrolled over the four ring slots");
+                const std::integral_constant<int, 0> b0; const std::integral_constant<int, 1> b1;
+                const std::integral_constant<int, 2> b2; const std::integral_constant<int, 3> b3;
+                int left = sp_total;
+                for (; left >= kSpRing; left -= kSpRing) { consume(b0); consume(b1); consume(b2); consume(b3); }
+                if (left > 0) {
+                    consume(b0);
+                    if (left > 1) { consume(b1); if (left > 2) consume(b2); }
                 }
             }
             flush();
