@@ -177,26 +177,9 @@ static_assert(kSpChunk == 8, "a chunk is one 256-bit value load and one 128-bit 
 
 // 256-bit loads carry their L2 eviction priority in the opcode (LDG.E.NA.ELL2.256 / .EFL2.256): no policy
 // register, no R2UR.  keep: 1 evict_last, 0 evict_first, -1 evict_normal.
-// Chunks [chunk0, chunk0 + n) of the stream held in shared memory for the whole launch (resident loop): values
-// as [chunk][half][lane] float4 (conflict-free 128-bit reads), offsets as [chunk][lane] uint4.
-struct SpRes {
-    unsigned int chunk0, n;
-    const float4* val;
-    const void* col;         // uint4 [chunk][lane] (16-bit offsets) or uint2 [chunk][lane] (8-bit column deltas)
-};
-
 template <bool C8>
-__device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpRes& res, unsigned int chunk, int lane, int keep, uint64_t pol_keep, uint64_t pol_stream)
+__device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, unsigned int chunk, int lane, int keep, uint64_t pol_keep, uint64_t pol_stream)
 {
-    const unsigned int rc = chunk - res.chunk0;
-    if (rc < res.n) {
-        const float4 lo = res.val[(rc * 2 + 0) * 32 + lane], hi = res.val[(rc * 2 + 1) * 32 + lane];
-        b.v[0] = __float_as_uint(lo.x); b.v[1] = __float_as_uint(lo.y); b.v[2] = __float_as_uint(lo.z); b.v[3] = __float_as_uint(lo.w);
-        b.v[4] = __float_as_uint(hi.x); b.v[5] = __float_as_uint(hi.y); b.v[6] = __float_as_uint(hi.z); b.v[7] = __float_as_uint(hi.w);
-        if (C8) { const uint2 c = reinterpret_cast<const uint2*>(res.col)[rc * 32 + lane]; b.c.x = c.x; b.c.y = c.y; }
-        else b.c = reinterpret_cast<const uint4*>(res.col)[rc * 32 + lane];
-        return;
-    }
     // Two policies: keep (evict_last) for what should stay in L2 from one iteration to the next -- all of a stream that
     // fits, else its pinned prefix -- and evict_first for the rest of a stream that does not fit.  (keep < 0, "no hints",
     // is a stream small enough not to care: kept.)  The 256-bit value loads carry the policy in the opcode; narrower
@@ -223,28 +206,12 @@ __device__ __forceinline__ void sp_load(SpBuf& b, const SparseDev& sp, const SpR
 // The resident loop's form of sp_load.  A chunk is named by `o`, THIS LANE's byte offset into the 8-bit column array,
 // (chunk * 32 + lane) * 8: the lane's values sit at 4 * o and its 16-bit column offsets at 2 * o, so that the request side
 // carries one running 32-bit number (+256 per chunk) instead of rebuilding two 64-bit addresses from a chunk index
-// (kSpMaxStepsO bounds the stream so that it fits).  The shared-memory head is the window [o0, o0 + on) of the same offsets.
+// (kSpMaxStepsO bounds the stream so that it fits).
 // KEEP_ALL: the whole stream fits in L2 -- one value load (evict_last in its opcode) and an unhinted column load, no
 // policy registers; otherwise the two policies of sp_load.
-struct SpResO {
-    unsigned int o0, on;
-    const unsigned char* val;    // [chunk][half][lane] float4
-    const unsigned char* col;    // [chunk][lane] uint2 (8-bit distances) or uint4 (16-bit offsets)
-};
 template <bool C8, bool KEEP_ALL>
-__device__ __forceinline__ void sp_load_at(SpBuf& b, const SparseDev& sp, const SpResO& res, unsigned int o, int lane, int keep, uint64_t pol_keep, uint64_t pol_stream)
+__device__ __forceinline__ void sp_load_at(SpBuf& b, const SparseDev& sp, unsigned int o, int keep, uint64_t pol_keep, uint64_t pol_stream)
 {
-    const unsigned int ro = o - res.o0;
-    if (ro < res.on) {
-        // ro = rc * 256 + lane * 8  ->  values at rc * 1024 + half * 512 + lane * 16 = 4 * ro - 16 * lane (+ 512)
-        const unsigned char* vp = res.val + (4u * ro - 16u * (unsigned int)lane);
-        const uint4 lo = *reinterpret_cast<const uint4*>(vp), hi = *reinterpret_cast<const uint4*>(vp + 512);
-        b.v[0] = lo.x; b.v[1] = lo.y; b.v[2] = lo.z; b.v[3] = lo.w;
-        b.v[4] = hi.x; b.v[5] = hi.y; b.v[6] = hi.z; b.v[7] = hi.w;
-        if (C8) { const uint2 c = *reinterpret_cast<const uint2*>(res.col + ro); b.c.x = c.x; b.c.y = c.y; }
-        else b.c = *reinterpret_cast<const uint4*>(res.col + 2u * ro);
-        return;
-    }
     const unsigned char* vp = reinterpret_cast<const unsigned char*>(sp.val) + (size_t)o * 4u;
     const unsigned char* cp = C8 ? reinterpret_cast<const unsigned char*>(sp.col8) + o
                                  : reinterpret_cast<const unsigned char*>(sp.col) + (size_t)o * 2u;
@@ -369,7 +336,7 @@ struct SpSeqGrid {
 // Put the first kSpRing chunks of a sequence in flight (ring slots 0 ..), e.g. for the NEXT iteration while the
 // barrier and the merge of this one run.
 template <bool C8, class SEQ>
-__device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, int lane, uint64_t pol_keep, uint64_t pol_stream)
+__device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SEQ& seq, int lane, uint64_t pol_keep, uint64_t pol_stream)
 {
     SpCursor p;
     p.k = seq.k_first;
@@ -377,7 +344,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 #pragma unroll
     for (int b = 0; b < kSpRing; ++b) {
         if (p.k < seq.k_end) {
-            sp_load<C8>(ring[b], sp, res, p.chunk0 + (unsigned int)p.c, lane, p.keep, pol_keep, pol_stream);
+            sp_load<C8>(ring[b], sp, p.chunk0 + (unsigned int)p.c, lane, p.keep, pol_keep, pol_stream);
             sp_next(p, seq);
         }
     }
@@ -388,7 +355,7 @@ __device__ __forceinline__ void sp_prefetch(SpBuf (&ring)[kSpRing], const Sparse
 // at the same speed -- the sweep is bound by the shared-memory gathers, not by loads in flight.)  begin(k) runs when a unit starts (row scalars), end(k, dot_hi, dot_lo) after its last chunk, with the
 // G-lane sums done.
 template <int G, bool C8, class SEQ, class BEGIN, class END>
-__device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SpRes& res, const SEQ& seq, const float2* s_hl, int lane,
+__device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev& sp, const SEQ& seq, const float2* s_hl, int lane,
                                          uint64_t pol_keep, uint64_t pol_stream, BEGIN begin, END end)
 {
     SpCursor cns, prd;
@@ -415,7 +382,7 @@ __device__ __forceinline__ void sp_sweep(SpBuf (&ring)[kSpRing], const SparseDev
                 sp_next(cns, seq);
                 more = cns.k < seq.k_end;
                 if (prd.k < seq.k_end) {
-                    sp_load<C8>(ring[b], sp, res, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, pol_keep, pol_stream);
+                    sp_load<C8>(ring[b], sp, prd.chunk0 + (unsigned int)prd.c, lane, prd.keep, pol_keep, pol_stream);
                     sp_next(prd, seq);
                 }
             }

@@ -368,8 +368,7 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
 
     // the stream does not depend on the pair: first chunks in flight before the dependency wait
     SpBuf ring[kSpRing];
-    const SpRes res{0u, 0u, nullptr, nullptr};      // nothing is kept on chip across kernel launches
-    if (a.early_load) sp_prefetch<C8>(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
+    if (a.early_load) sp_prefetch<C8>(ring, a.sp, seq, lane, pol_keep, pol_stream);
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
@@ -390,12 +389,12 @@ __global__ void __launch_bounds__(kPassThreads, 2) smo_pass_sparse_kernel(const 
         s_hl[4 * i + 3] = make_float2(h.w, l.w);
     }
     __syncthreads();
-    if (!a.early_load) sp_prefetch<C8>(ring, a.sp, res, seq, lane, pol_keep, pol_stream);
+    if (!a.early_load) sp_prefetch<C8>(ring, a.sp, seq, lane, pol_keep, pol_stream);
 
     float e_xsq = 0.f, e_f = 0.f, e_alpha = 0.f;
     int e_y = 0, erow = 0;
     bool eown = false;
-    sp_sweep<G, C8>(ring, a.sp, res, seq, s_hl, lane, pol_keep, pol_stream,
+    sp_sweep<G, C8>(ring, a.sp, seq, s_hl, lane, pol_keep, pol_stream,
         [&](int k) {
             erow = seq.local(k) * GROUPS + grp;
             eown = (sub == 0) && (erow < a.n);

@@ -58,7 +58,6 @@ struct SparseDev {
     int max_cta_units;          // largest cta_first[i+1] - cta_first[i]
     unsigned int total_steps;
     unsigned int pin_steps;     // filled by the launcher: steps per CTA loaded L2::evict_last
-    unsigned int res_chunks;    // filled by the launcher (resident loop): chunks per CTA kept in shared memory
 };
 
 // Arguments of the fused pass kernel (by value; small enough for the parameter space).

@@ -160,9 +160,8 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
     // ... the units each warp slot sweeps (SparseDev::perm, cnt) ...
     unsigned short* s_perm = reinterpret_cast<unsigned short*>(s_uoff + ((a.sp.max_cta_units + 1 + 3) & ~3));
     unsigned short* s_cnt = s_perm + ((a.sp.perm_stride + 7) & ~7);
-    // ... then the first chunks of this CTA's part of the stream, kept on chip for the whole launch
-    float4* s_rval = reinterpret_cast<float4*>(s_cnt + 16);
-    uint2* s_rcol = reinterpret_cast<uint2*>(s_rval + (size_t)a.sp.res_chunks * 64);      // uint4 per lane and chunk in the 16-bit format
+    // (The stream itself stays in L2: a head of it held in shared memory for the whole launch, as the dense sweep holds
+    // rows, cost the sweep more in per-chunk instructions than the L2 reads it saved -- measured at 15 000 to 60 000 rows.)
     // their per-row scalars live on chip as well (a warp round on a stationary unit then touches no
     // global memory at all): |x|^2, y, f, alpha -- [a.res_units * RPW] each, after the rows
     float* s_rxsq = reinterpret_cast<float*>(s_x + (size_t)a.res_units * RPW * a.pitch4);
@@ -284,24 +283,10 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
         a_hi_old = a.alpha[i_hi - a.index_base];
         a_lo_old = a.alpha[i_lo - a.index_base];
     }
-    SpResO sp_res{0u, 0u, reinterpret_cast<const unsigned char*>(s_rval), reinterpret_cast<const unsigned char*>(s_rcol)};
     if (SPARSE) {
         for (int i = tid; i <= u1 - u0; i += kResThreads) s_uoff[i] = a.sp.unit_off[u0 + i];
         for (int i = tid; i < a.sp.perm_stride; i += kResThreads) s_perm[i] = a.sp.perm[(size_t)cta * a.sp.perm_stride + i];
         if (tid < NW) s_cnt[tid] = a.sp.cnt[cta * NW + tid];
-        const unsigned int c_first = a.sp.unit_off[u0] / kSpChunk, c_end = a.sp.unit_off[u1] / kSpChunk;
-        const unsigned int res_n = min(c_end - c_first, a.sp.res_chunks);
-        sp_res.o0 = c_first * 256u;                      // offsets as sp_load_at counts them: 256 per chunk
-        sp_res.on = res_n * 256u;
-        const float4* gv = reinterpret_cast<const float4*>(a.sp.val) + (size_t)c_first * 64;      // [chunk][lane][2 x float4]
-        const int col_u2 = C8 ? 1 : 2;                   // 8-byte words of column data per lane and chunk
-        const uint2* gc = C8 ? reinterpret_cast<const uint2*>(a.sp.col8) + (size_t)c_first * 32
-                             : reinterpret_cast<const uint2*>(a.sp.col) + (size_t)c_first * 64;
-        for (unsigned int i = tid; i < res_n * 64u; i += kResThreads) {
-            const unsigned int rc = i >> 6, half = (i >> 5) & 1u, ln = i & 31u;
-            s_rval[i] = ldg_stream4(gv + (size_t)(rc * 32u + ln) * 2u + half);
-        }
-        for (unsigned int i = tid; i < res_n * 32u * col_u2; i += kResThreads) s_rcol[i] = __ldg(gc + i);
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int i = a.pitch4 + tid; i < CAP4; i += kResThreads) { s_hi[i] = z; s_lo[i] = z; }
     } else {
@@ -606,11 +591,11 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
             sp_pj = 0;
             if (sp_cnt > 0) sp_open();
         };
-        auto sp_request = [&](int b) {               // next chunk of the sequence -> ring slot b (no-op once the list is exhausted)
-            if (sp_pj < sp_cnt) {
+        auto sp_request = [&](int b, bool sure = false) {    // next chunk of the sequence -> ring slot b (no-op once the list is exhausted;
+            if (sure || sp_pj < sp_cnt) {                    //  sure: the caller knows that it is not)
                 const bool last = --sp_left == 0;
                 sp_tag[b] = last ? sp_utag : 0u;
-                sp_load_at<C8, KEEP_ALL>(sp_ring[b], a.sp, sp_res, sp_po, lane, sp_pkeep, pol_keep, pol_stream);
+                sp_load_at<C8, KEEP_ALL>(sp_ring[b], a.sp, sp_po, sp_pkeep, pol_keep, pol_stream);
                 sp_po += 256u;
                 if (last) { if (++sp_pj < sp_cnt) sp_open(); }
             }
@@ -650,11 +635,12 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                 asm volatile("" : "+r"(pos0));   // held in a register: rebuilt from the CTA's shared window it costs a special-register read per chunk
                 unsigned int pos = pos0;         // 8-bit format: shared-memory address of this lane's current column in s_hl
                 float acc_hi = 0.f, acc_lo = 0.f;
-                auto consume = [&](auto slot) {
+                auto consume = [&](auto slot, auto req) {
                     constexpr int b = decltype(slot)::value;
+                    constexpr int REQ = decltype(req)::value;        // 2: a chunk kSpRing ahead exists; 1: it may; 0: it does not
                     const unsigned int tag = sp_tag[b];
                     sp_fma<C8, 4>(sp_ring[b], s_hl, acc_hi, acc_lo, pos);
-                    sp_request(b);               // the consumed slot takes the chunk kSpRing ahead at once
+                    if constexpr (REQ > 0) sp_request(b, REQ == 2);  // the consumed slot takes the chunk kSpRing ahead at once
                     if (tag & kTagLast) {
                         const int unit_row0 = (int)(tag & kTagRow);
                         sp_group_sum<SGL>(acc_hi, acc_lo);
@@ -674,15 +660,18 @@ __global__ void __launch_bounds__(kResThreads, 1) smo_resident_kernel(const Resi
                         pos = pos0;              // the next chunk starts a unit: column distances count from column 0 again
                     }
                 };
-                // whole rounds of the ring without a per-chunk end test, then the up to three chunks left
+                // Whole rounds of the ring without per-chunk end tests -- while at least two rounds are left every request
+                // is for a chunk that exists -- then one round whose requests may run off the list, then the up to three
+                // chunks left, which request nothing.
                 static_assert(kSpRing == 4, "the sweep is unrolled over the four ring slots");
-                const std::integral_constant<int, 0> b0; const std::integral_constant<int, 1> b1;
-                const std::integral_constant<int, 2> b2; const std::integral_constant<int, 3> b3;
+                const std::integral_constant<int, 0> b0, none; const std::integral_constant<int, 1> b1, maybe;
+                const std::integral_constant<int, 2> b2, sure; const std::integral_constant<int, 3> b3;
                 int left = sp_total;
-                for (; left >= kSpRing; left -= kSpRing) { consume(b0); consume(b1); consume(b2); consume(b3); }
+                for (; left >= 2 * kSpRing; left -= kSpRing) { consume(b0, sure); consume(b1, sure); consume(b2, sure); consume(b3, sure); }
+                if (left >= kSpRing) { consume(b0, maybe); consume(b1, maybe); consume(b2, maybe); consume(b3, maybe); left -= kSpRing; }
                 if (left > 0) {
-                    consume(b0);
-                    if (left > 1) { consume(b1); if (left > 2) consume(b2); }
+                    consume(b0, none);
+                    if (left > 1) { consume(b1, none); if (left > 2) consume(b2, none); }
                 }
             }
             flush();
@@ -1042,7 +1031,6 @@ static cudaError_t launch_resident_sparse_k(ResidentDev a, int variant, cudaStre
     constexpr int CAP4 = 256;
     static_assert(CAP4 * 4 == kSparseMaxPitch, "selected-row buffers cover the widest sparse row");
     auto kernel = smo_resident_kernel<32, 8, SG, C8, KEEP_ALL>;
-    constexpr size_t kChunkBytes = C8 ? 1280 : 1536;         // 32 lanes x 8 steps x (4 + 1 or 2) bytes
     static ResCfg s_cache[kMaxDevices];
     static std::mutex s_mu;
     ResCfg cfg;
@@ -1056,15 +1044,7 @@ static cudaError_t launch_resident_sparse_k(ResidentDev a, int variant, cudaStre
     const size_t fixed = 2 * (size_t)CAP4 * 16 + (size_t)a.pitch4 * 4 * 128 + (((size_t)a.sp.max_cta_units + 1 + 3) & ~(size_t)3) * sizeof(unsigned int) +
                          (((size_t)a.sp.perm_stride + 7) & ~(size_t)7) * sizeof(unsigned short) + 16 * sizeof(unsigned short);
     if (fixed > (size_t)s_smem_max) return cudaErrorInvalidValue;
-    // the rest of shared memory holds the head of each CTA's part of the stream (1.25 or 1.5 KB per chunk)
-    size_t res_bytes = (size_t)s_smem_max - fixed;
-    {
-        static const char* cap_env = getenv("DPSVM_SP_RES_KB");      // tuning aid: cap the on-chip part
-        if (cap_env && *cap_env) { const size_t cap = (size_t)atoi(cap_env) * 1024; if (cap < res_bytes) res_bytes = cap; }
-    }
-    const size_t per_cta_chunks = ((size_t)a.sp.total_steps / kSpChunk + s_grid - 1) / s_grid + 64;    // no CTA holds more
-    a.sp.res_chunks = (unsigned int)std::min(res_bytes / kChunkBytes, per_cta_chunks);
-    const size_t smem = fixed + (size_t)a.sp.res_chunks * kChunkBytes;
+    const size_t smem = fixed;
     a.res_units = 0;
     a.pin_units = 0;
     const bool hint = (variant & 2) != 0;

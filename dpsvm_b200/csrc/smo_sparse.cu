@@ -483,7 +483,7 @@ int sparse_setup(dpsvm_ctx* c)
     sp.col8 = use_col8 ? c->d_sp_col8 : nullptr;
     sp.step_bytes = use_col8 ? 160 : 192;
     sp.lanes = lanes; sp.n_units = n_units; sp.grid = grid; sp.max_cta_units = max_units;
-    sp.total_steps = total_steps; sp.pin_steps = 0; sp.res_chunks = 0;
+    sp.total_steps = total_steps; sp.pin_steps = 0;
     sp.perm = c->d_sp_perm; sp.cnt = c->d_sp_perm + h_perm.size(); sp.perm_stride = perm_stride;
     c->sp = sp;
     return DPSVM_OK;
