@@ -12,6 +12,6 @@ CMD="env $ENVP python bench.py --steps 2 --warmup 3 --e2e-steps 1 --converge 0 -
 $CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.err; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "launch list rc=$?"
-ncu --set full --clock-control none --cache-control none --import-source on -k regex:${KRE} -s 4 -c 2 -o gpurun_out/${TAG}_full -f $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
+ncu --set full --clock-control none --cache-control none --import-source on -k regex:${KRE} -s 4 -c 1 -o gpurun_out/${TAG}_full -f $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "full capture rc=$?"
 ls -la gpurun_out | grep ${TAG}
