@@ -150,11 +150,13 @@ def workload_config(args, n_total, d, prm):
     }
 
 
-def algorithmic_bytes(n, d, cache_lines, nnz=None):
+def algorithmic_bytes(n, d, cache_lines, nnz=None, sweep_bytes=0):
     """X shard once + |x|^2, f read, f write, alpha, y at 4 B each (logical d); the two
     cache-line stores of a miss/miss iteration add 8 n when the kernel-row cache is on.
-    nnz given (sparse stream): X costs 6 B per non-zero (fp32 value + 16-bit column), padding excluded."""
-    x_bytes = 4.0 * n * d if nnz is None else 6.0 * nnz
+    nnz given (sparse stream): X costs 5 or 6 B per non-zero (fp32 value + 8-bit column distance or 16-bit column
+    offset), padding excluded.  A padded stream of fewer than 6 B per non-zero can only be the 8-bit format."""
+    per_nz = 5.0 if (nnz and 0 < sweep_bytes < 6.0 * nnz) else 6.0
+    x_bytes = 4.0 * n * d if nnz is None else per_nz * nnz
     return x_bytes + 20.0 * n + (8.0 * n if cache_lines >= 2 else 0.0)
 
 
@@ -552,7 +554,7 @@ def main():
         return
 
     peak, peak_src = measured_peak()
-    stream_abytes = algorithmic_bytes(n_shard, d, args.cache_size, nnz if lanes else None)
+    stream_abytes = algorithmic_bytes(n_shard, d, args.cache_size, nnz if lanes else None, sweep_bytes)
     dense_abytes = algorithmic_bytes(n_shard, d, args.cache_size)
     iter_ms = ms / max(done_iters, 1)
     traffic, traffic_src = None, None
@@ -622,8 +624,8 @@ def main():
                      "frac_dense_basis": achieved / peak,
                      "frac_stream_basis": (achieved_stream / peak) if lanes else None,
                      "stream_bytes_per_iteration": stream_abytes if lanes else None,
-                     "note": ("the sweep reads the sparse stream (6 B per non-zero, zeros skipped), so on the dense-row basis the figure can exceed "
-                              "the HBM peak; a stream of up to ~120 MB is served from L2 and shared memory and the binding units are the "
+                     "note": ("the sweep reads the sparse stream (5 or 6 B per non-zero, zeros skipped), so on the dense-row basis the figure can exceed "
+                              "the HBM peak; a stream of up to ~120 MB is served from L2 and the busiest units are the "
                               "shared-memory gathers (LSU) and the L2->SM fabric, not HBM -- `bound` says which; frac_stream_basis counts only "
                               "the bytes the kernel is asked to read") if lanes else
                              ("the whole shard is held in shared memory across iterations: nothing streams from HBM" if on_chip else None),
