@@ -32,3 +32,16 @@ def test_reference_arm_prints_one_contract_line():
 def test_reference_arm_other_ranks_exit_quietly():
     r = _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_algorithmic_bytes_are_survey_8d():
+    """roofline.achieved is built from these: 4 n d + 20 n per iteration, + 8 n of cache-line stores when
+    the kernel-row cache is on; the sparse stream's own basis counts 6 B per non-zero, 5 B with 8-bit column distances."""
+    sys.path.insert(0, ROOT)
+    import bench
+    n, d, nnz = 60000, 784, 18223215
+    assert bench.algorithmic_bytes(n, d, 0) == 4 * n * d + 20 * n
+    assert bench.algorithmic_bytes(n, d, 10) == 189840000                    # the figure DESIGN.md / BASELINE.md quote
+    assert bench.algorithmic_bytes(n, d, 10, nnz) == 6 * nnz + 28 * n
+    assert bench.algorithmic_bytes(n, d, 10, nnz, sweep_bytes=int(5 * nnz * 1.125)) == 5 * nnz + 28 * n
+    assert bench.algorithmic_bytes(n, d, 10, nnz, sweep_bytes=int(6 * nnz * 1.125)) == 6 * nnz + 28 * n
