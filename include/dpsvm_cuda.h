@@ -171,7 +171,8 @@ typedef struct {
 #define DPSVM_FLAG_DENSE 8           /* the sweep always reads the dense rows (what the reference's cublasSgemv does,
                                         svmTrain.cu:222,247) */
 #define DPSVM_FLAG_SPARSE 16         /* the sweep always reads the sparse stream of the owned rows (rows of at most
-                                        1024 floats).  Neither flag: decided per upload from the share of non-zeros.
+                                        1024 floats, fewer than 2^27 steps of 32 non-zero slots per shard: DPSVM_ERR_LIMIT
+                                        at upload otherwise).  Neither flag: decided per upload from the share of non-zeros.
                                         The two layouts add the same non-zero products in a different, fixed order
                                         (see dpsvm_layout_info); results agree to fp32 rounding of the dot products. */
 
